@@ -1,0 +1,108 @@
+/*
+ * TEST INFRASTRUCTURE — C entry points around the UNMODIFIED reference headers.
+ *
+ * Compiled by oracle/Makefile from the sources where they lie under $(REFERENCE_DIR)
+ * (default /root/reference) into oracle/_ref/libref_auction.so.  Nothing of the reference is
+ * copied: this file only instantiates LSAP::Auction / LSAP::AuctionMT (Auction.h:44,
+ * AuctionMT.h:50) on Eigen matrices it fills from plain pointers, and flattens the
+ * returned Edges (AuctionCommon.h:30-40).  Never built with -DDEBUG_AUCTION.
+ *
+ * The reference has no error path: rows > cols or an all-zero row never return
+ * (SURVEY.md §0.5).  Callers keep to rows <= cols and strictly positive inputs.
+ */
+#include <thread>
+
+#include "AuctionAlgorithm/Auction.h"
+#include "AuctionAlgorithm/AuctionMT.h"
+
+#include <cstdint>
+#include <cstring>
+
+namespace
+{
+
+template <typename S> using Mat = Eigen::Matrix<S, -1, -1>;
+
+template <typename S> Mat<S> to_eigen(const S* a, int64_t rows, int64_t cols, int64_t ld, int layout)
+{
+    Mat<S> m(rows, cols);
+    for (int64_t j = 0; j < cols; j++)
+        for (int64_t i = 0; i < rows; i++)
+            m(i, j) = layout ? a[i * ld + j] : a[i + j * ld];
+    return m;
+}
+
+template <typename S, typename Edges>
+int64_t flatten(const Edges& e, int64_t* ex, int64_t* ey, S* ev)
+{
+    int64_t n = 0;
+    for (const auto& edge : e)
+    {
+        ex[n] = (int64_t)edge.x;
+        ey[n] = (int64_t)edge.y;
+        ev[n] = edge.v;
+        n++;
+    }
+    return n;
+}
+
+} // namespace
+
+extern "C" {
+
+/* returns the number of edges; seconds_out (nullable) = wall time of solve() alone, the
+ * region the reference's own driver times (LSAP.cpp:44). */
+int64_t ref_auction_f64(const double* a, int64_t rows, int64_t cols, int64_t ld, int layout, int64_t* ex,
+                        int64_t* ey, double* ev, double* seconds_out)
+{
+    const Mat<double> m = to_eigen<double>(a, rows, cols, ld, layout);
+    const auto t0 = std::chrono::steady_clock::now();
+    const auto edges = LSAP::Auction<double>::solve(m);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+    return flatten<double>(edges, ex, ey, ev);
+}
+
+int64_t ref_auction_f32(const float* a, int64_t rows, int64_t cols, int64_t ld, int layout, int64_t* ex,
+                        int64_t* ey, float* ev, double* seconds_out)
+{
+    const Mat<float> m = to_eigen<float>(a, rows, cols, ld, layout);
+    const auto t0 = std::chrono::steady_clock::now();
+    const auto edges = LSAP::Auction<float, Eigen::MatrixXf>::solve(m);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+    return flatten<float>(edges, ex, ey, ev);
+}
+
+int64_t ref_auctionmt_f64(const double* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                          int64_t n_threads, int64_t* ex, int64_t* ey, double* ev, double* seconds_out)
+{
+    const Mat<double> m = to_eigen<double>(a, rows, cols, ld, layout);
+    const auto t0 = std::chrono::steady_clock::now();
+    const auto edges = LSAP::AuctionMT<double>::solve(m, (size_t)n_threads);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+    return flatten<double>(edges, ex, ey, ev);
+}
+
+/* fp32 data widened exactly to double, then Auction<double>: the oracle instantiation for
+ * every fp32 config. */
+int64_t ref_auction_f32_as_f64(const float* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                               int64_t* ex, int64_t* ey, double* ev, double* seconds_out)
+{
+    Mat<double> m(rows, cols);
+    for (int64_t j = 0; j < cols; j++)
+        for (int64_t i = 0; i < rows; i++)
+            m(i, j) = (double)(layout ? a[i * ld + j] : a[i + j * ld]);
+    const auto t0 = std::chrono::steady_clock::now();
+    const auto edges = LSAP::Auction<double>::solve(m);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+    return flatten<double>(edges, ex, ey, ev);
+}
+
+} // extern "C"

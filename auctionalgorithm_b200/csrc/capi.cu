@@ -1,0 +1,809 @@
+// capi.cu — libb200lsap.so: handle, device buffers and the extern "C" entry points declared in
+// include/b200lsap.h.  Host-side controller work that the reference does in
+// Auction<Scalar>::solve (Auction.h:44-58: eps, initial prices, locks) is done here; the rounds
+// themselves run in dense_kernels.cuh / batch_kernels.cuh.  There is no CPU solve path.
+#include "../../include/b200lsap.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "batch_kernels.cuh"
+#include "dense_kernels.cuh"
+
+using namespace b200lsap;
+
+namespace
+{
+
+struct DevBuf
+{
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap)
+            return cudaSuccess;
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        bytes = (bytes + 255) & ~size_t(255);
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess)
+            cap = bytes;
+        return e;
+    }
+    void release()
+    {
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename U> U* as() const { return static_cast<U*>(p); }
+};
+
+} // namespace
+
+struct b200lsap_handle
+{
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    DevBuf a, staging, prices, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
+        ctrl, out64, batch_in, batch_out;
+    DenseCtrl* h_ctrl = nullptr; // pinned mirror
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    int64_t last_cols = 0; // prices of the last dense solve are valid for this many columns
+    int min_seg = 512;
+    int64_t launches = 0;
+};
+
+namespace
+{
+
+int fail(b200lsap_handle* h, int status, const char* what, cudaError_t e = cudaSuccess)
+{
+    if (h)
+    {
+        h->err = what;
+        if (e != cudaSuccess)
+        {
+            h->err += ": ";
+            h->err += cudaGetErrorString(e);
+        }
+    }
+    return status;
+}
+
+#define CU(call)                                                                                                   \
+    do                                                                                                             \
+    {                                                                                                              \
+        cudaError_t e_ = (call);                                                                                   \
+        if (e_ != cudaSuccess)                                                                                     \
+            return fail(h, B200LSAP_ERR_CUDA, #call, e_);                                                          \
+    } while (0)
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+inline int grid_for(const b200lsap_handle* h, int64_t work_items, int per_block)
+{
+    int64_t g = (work_items + per_block - 1) / per_block;
+    const int64_t cap = (int64_t)h->num_sms * 8;
+    if (g > cap)
+        g = cap;
+    if (g < 1)
+        g = 1;
+    return (int)g;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* b200lsap_status_string(int status)
+{
+    switch (status)
+    {
+    case B200LSAP_OK: return "ok";
+    case B200LSAP_ERR_SHAPE: return "bad shape: need 1 <= rows <= cols and ld >= minor dimension";
+    case B200LSAP_ERR_INFEASIBLE: return "infeasible: a row has no non-zero coefficient";
+    case B200LSAP_ERR_MAX_ROUNDS: return "round watchdog expired";
+    case B200LSAP_ERR_CUDA: return "CUDA error";
+    case B200LSAP_ERR_ARG: return "bad argument";
+    case B200LSAP_ERR_NO_DEVICE: return "no CUDA device";
+    default: return "unknown status";
+    }
+}
+
+const char* b200lsap_last_error(const b200lsap_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+void b200lsap_options_default(b200lsap_options* o)
+{
+    if (!o)
+        return;
+    memset(o, 0, sizeof *o);
+    o->eps_multiplier = 1e-5;
+    o->eps_scaling = -1;
+    o->eps_start = 0.0;
+    o->eps_factor = 0.0;
+    o->max_rounds = 0;
+    o->driver = 0;
+}
+
+int b200lsap_create(b200lsap_handle** out, int device)
+{
+    if (!out)
+        return B200LSAP_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+        return B200LSAP_ERR_NO_DEVICE;
+    if (device < 0 && cudaGetDevice(&device) != cudaSuccess)
+        return B200LSAP_ERR_NO_DEVICE;
+    if (device >= n)
+        return B200LSAP_ERR_ARG;
+    b200lsap_handle* h = new b200lsap_handle();
+    h->device = device;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMallocHost((void**)&h->h_ctrl, sizeof(DenseCtrl)) != cudaSuccess)
+    {
+        delete h;
+        return B200LSAP_ERR_CUDA;
+    }
+    h->own_stream = true;
+    for (auto& e : h->ev)
+        cudaEventCreate(&e);
+    if (const char* s = getenv("B200LSAP_MIN_SEG"))
+    {
+        int v = atoi(s);
+        if (v >= 128)
+            h->min_seg = (v + 127) & ~127;
+    }
+    *out = h;
+    return B200LSAP_OK;
+}
+
+int b200lsap_destroy(b200lsap_handle* h)
+{
+    if (!h)
+        return B200LSAP_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
+                      &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
+                      &h->batch_out})
+        b->release();
+    for (auto& e : h->ev)
+        if (e)
+            cudaEventDestroy(e);
+    if (h->h_ctrl)
+        cudaFreeHost(h->h_ctrl);
+    if (h->own_stream && h->stream)
+        cudaStreamDestroy(h->stream);
+    delete h;
+    return B200LSAP_OK;
+}
+
+int b200lsap_set_stream(b200lsap_handle* h, void* s)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->own_stream && h->stream)
+        cudaStreamDestroy(h->stream);
+    h->stream = static_cast<cudaStream_t>(s);
+    h->own_stream = false;
+    return B200LSAP_OK;
+}
+
+void* b200lsap_host_alloc(int64_t bytes)
+{
+    void* p = nullptr;
+    if (bytes <= 0 || cudaMallocHost(&p, (size_t)bytes) != cudaSuccess)
+        return nullptr;
+    return p;
+}
+
+void b200lsap_host_free(void* p)
+{
+    if (p)
+        cudaFreeHost(p);
+}
+
+} // extern "C"
+
+// =============================================================================================
+// Dense solve
+// =============================================================================================
+namespace
+{
+
+struct DensePlan
+{
+    int64_t rows, cols, ldp;
+    std::vector<double> eps;
+    int64_t max_rounds;
+    int driver;
+};
+
+// eps schedule (the controller constants of Auction.h:54-55, plus optional scaling).
+int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_options* opts, DensePlan& plan)
+{
+    b200lsap_options o;
+    b200lsap_options_default(&o);
+    if (opts)
+        o = *opts;
+    if (!(o.eps_multiplier > 0))
+        return fail(h, B200LSAP_ERR_ARG, "eps_multiplier must be positive");
+    const double eps_final = o.eps_multiplier / (double)cols; // Auction.h:55
+    bool scaling = o.eps_scaling < 0 ? (rows == cols) : (o.eps_scaling != 0);
+    if (scaling && rows != cols)
+        return fail(h, B200LSAP_ERR_ARG,
+                    "eps scaling needs rows == cols: a forward-only auction with scaled eps is not optimal on "
+                    "asymmetric problems (SURVEY.md section 7.3)");
+    plan.eps.clear();
+    if (scaling)
+    {
+        double e = o.eps_start > 0 ? o.eps_start : 0.25;
+        const double f = o.eps_factor > 1 ? o.eps_factor : 5.0;
+        while (e > eps_final * 1.0000001 && (int)plan.eps.size() < kMaxPhases - 1)
+        {
+            plan.eps.push_back(e);
+            e /= f;
+        }
+    }
+    plan.eps.push_back(eps_final);
+    plan.rows = rows;
+    plan.cols = cols;
+    plan.max_rounds = o.max_rounds > 0 ? o.max_rounds : 20000000;
+    plan.driver = o.driver;
+    return B200LSAP_OK;
+}
+
+template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t cols, int64_t ldp, int total_warps)
+{
+    CU(h->prices.ensure((ldp + 512) * sizeof(double)));
+    CU(h->profits.ensure(rows * sizeof(double)));
+    CU(h->slots.ensure(cols * sizeof(BidSlot)));
+    CU(h->owner.ensure(cols * sizeof(int)));
+    CU(h->row2col.ensure(rows * sizeof(int)));
+    CU(h->bid_col.ensure(rows * sizeof(int)));
+    CU(h->bid_val.ensure(rows * sizeof(double)));
+    CU(h->list0.ensure(rows * sizeof(int)));
+    CU(h->list1.ensure(rows * sizeof(int)));
+    CU(h->partial.ensure((size_t)(total_warps + 64) * sizeof(Top2<T>)));
+    CU(h->arrive.ensure(rows * sizeof(int)));
+    CU(h->ctrl.ensure(sizeof(DenseCtrl)));
+    return B200LSAP_OK;
+}
+
+template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, int64_t rows, int64_t cols, int64_t ld)
+{
+    DenseState<T> s;
+    s.A = A;
+    s.ld = ld;
+    s.rows = (int)rows;
+    s.cols = (int)cols;
+    s.cols4 = (int)round_up(cols, 4);
+    s.prices = h->prices.as<double>();
+    s.profits = h->profits.as<double>();
+    s.slots = h->slots.as<BidSlot>();
+    s.owner = h->owner.as<int>();
+    s.row2col = h->row2col.as<int>();
+    s.bid_col = h->bid_col.as<int>();
+    s.bid_val = h->bid_val.as<double>();
+    s.list[0] = h->list0.as<int>();
+    s.list[1] = h->list1.as<int>();
+    s.partial = h->partial.as<Top2<T>>();
+    s.arrive = h->arrive.as<int>();
+    s.ctrl = h->ctrl.as<DenseCtrl>();
+    s.min_seg = h->min_seg;
+    s.dry = 0;
+    return s;
+}
+
+template <typename T> int persistent_grid(b200lsap_handle* h, int& grid)
+{
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_auction_persistent<T>, kThreads, 0));
+    if (per_sm < 1)
+        return fail(h, B200LSAP_ERR_CUDA, "persistent kernel does not fit on an SM");
+    grid = h->num_sms; // one CTA per SM
+    return B200LSAP_OK;
+}
+
+// Runs the auction on a padded row-major device matrix.  On return h->row2col holds the
+// assignment and h->h_ctrl the controller block.
+template <typename T>
+int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan, b200lsap_stats* stats)
+{
+    int grid = 0;
+    int rc = persistent_grid<T>(h, grid);
+    if (rc)
+        return rc;
+    const int total_warps = grid * kWarpsPerBlock;
+    rc = alloc_state<T>(h, plan.rows, plan.cols, ld, total_warps);
+    if (rc)
+        return rc;
+    DenseState<T> s = bind_state<T>(h, A, plan.rows, plan.cols, ld);
+
+    DenseCtrl* hc = h->h_ctrl;
+    memset(hc, 0, sizeof *hc);
+    hc->count[0] = (int)plan.rows;
+    hc->n_phases = (int)plan.eps.size();
+    hc->max_rounds = plan.max_rounds;
+    for (size_t k = 0; k < plan.eps.size(); k++)
+        hc->eps[k] = plan.eps[k];
+    CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
+
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_init<T><<<grid, kThreads, 0, h->stream>>>(s, 0);
+    h->launches++;
+    if (plan.driver == 0)
+    {
+        void* args[] = {&s};
+        CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads), args, 0,
+                                       h->stream));
+        h->launches++;
+        CU(cudaEventRecord(h->ev[2], h->stream));
+        CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    else
+    {
+        // host-driven rounds: same device functions, the controller loop of Auction.h:60-100 here
+        int cur = 0, phase = 0;
+        long long rounds = 0, bids = 0;
+        for (;;)
+        {
+            CU(cudaMemcpyAsync(hc, s.ctrl, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            const int n = hc->count[cur];
+            if (hc->status != 0)
+                break;
+            if (n == 0)
+            {
+                if (phase + 1 >= (int)plan.eps.size())
+                    break;
+                phase++;
+                k_reset<T><<<grid, kThreads, 0, h->stream>>>(s, cur);
+                h->launches++;
+                continue;
+            }
+            if (rounds >= plan.max_rounds)
+            {
+                hc->status = B200LSAP_ERR_MAX_ROUNDS;
+                break;
+            }
+            k_bid<T><<<grid, kThreads, 0, h->stream>>>(s, cur, n, plan.eps[phase]);
+            k_resolve<T><<<grid, kThreads, 0, h->stream>>>(s, cur, n);
+            h->launches += 2;
+            cur ^= 1;
+            rounds++;
+            bids += n;
+        }
+        CU(cudaEventRecord(h->ev[2], h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        hc->rounds = rounds;
+        hc->bids = bids;
+        hc->phase = phase;
+    }
+    CU(cudaGetLastError());
+    h->last_cols = plan.cols;
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+        stats->ms_solve = ms;
+        stats->rounds = hc->rounds;
+        stats->bids = hc->bids;
+        stats->phases = hc->phase + 1;
+        stats->bid_bytes = hc->bids * plan.cols * (int64_t)sizeof(T);
+        stats->eps_final = plan.eps.back();
+    }
+    if (hc->status != 0)
+        return fail(h, hc->status, b200lsap_status_string(hc->status));
+    return B200LSAP_OK;
+}
+
+int check_shape(b200lsap_handle* h, const void* a, int64_t rows, int64_t cols, int64_t ld, int layout)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (!a)
+        return fail(h, B200LSAP_ERR_ARG, "null matrix");
+    if (layout != B200LSAP_COL_MAJOR && layout != B200LSAP_ROW_MAJOR)
+        return fail(h, B200LSAP_ERR_ARG, "layout must be 0 (column-major) or 1 (row-major)");
+    if (rows < 1 || cols < 1 || rows > cols || cols > 0x7fff0000ll || ld < (layout ? cols : rows))
+        return fail(h, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    return B200LSAP_OK;
+}
+
+// Brings the caller's matrix into the padded row-major device layout.  Returns the device
+// pointer to scan (the caller's own buffer when it already has that layout).
+template <typename T>
+int stage_matrix(b200lsap_handle* h, const T* a, bool on_host, int64_t rows, int64_t cols, int64_t ld, int layout,
+                 const T** A_out, int64_t* ld_out)
+{
+    const int64_t ldp = round_up(cols, 32);
+    if (!on_host && layout == B200LSAP_ROW_MAJOR && ld % 4 == 0 && cols % 4 == 0 && ((uintptr_t)a & 15) == 0)
+    {
+        *A_out = a;
+        *ld_out = ld;
+        return B200LSAP_OK;
+    }
+    CU(h->a.ensure((size_t)rows * ldp * sizeof(T)));
+    T* A = h->a.as<T>();
+    if (layout == B200LSAP_ROW_MAJOR)
+    {
+        if (on_host)
+        {
+            CU(cudaMemcpy2DAsync(A, ldp * sizeof(T), a, ld * sizeof(T), cols * sizeof(T), rows, cudaMemcpyHostToDevice,
+                                 h->stream));
+            if (ldp > cols)
+                CU(cudaMemset2DAsync(A + cols, ldp * sizeof(T), 0, (ldp - cols) * sizeof(T), rows, h->stream));
+        }
+        else
+        {
+            k_copy_pad<T><<<grid_for(h, rows * ldp, 256 * 8), 256, 0, h->stream>>>(a, ld, A, ldp, (int)rows, (int)cols);
+            h->launches++;
+        }
+    }
+    else
+    {
+        const T* src = a;
+        int64_t ld_src = ld;
+        if (on_host)
+        {
+            CU(h->staging.ensure((size_t)rows * cols * sizeof(T)));
+            CU(cudaMemcpy2DAsync(h->staging.p, rows * sizeof(T), a, ld * sizeof(T), rows * sizeof(T), cols,
+                                 cudaMemcpyHostToDevice, h->stream));
+            src = h->staging.as<T>();
+            ld_src = rows;
+        }
+        const int64_t tiles = ((rows + 31) / 32) * (ldp / 32);
+        k_transpose_pad<T><<<grid_for(h, tiles, 1), 256, 0, h->stream>>>(src, ld_src, A, ldp, (int)rows, (int)cols);
+        h->launches++;
+    }
+    CU(cudaGetLastError());
+    *A_out = A;
+    *ld_out = ldp;
+    return B200LSAP_OK;
+}
+
+template <typename T>
+int solve_host(b200lsap_handle* h, const T* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+               const b200lsap_options* opts, int64_t* row_to_col, double* prices_out, b200lsap_stats* stats)
+{
+    int rc = check_shape(h, a, rows, cols, ld, layout);
+    if (rc)
+        return rc;
+    if (!row_to_col)
+        return fail(h, B200LSAP_ERR_ARG, "null row_to_col");
+    CU(cudaSetDevice(h->device));
+    DensePlan plan;
+    rc = make_plan(h, rows, cols, opts, plan);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    h->launches = 0;
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    const T* A = nullptr;
+    int64_t ldA = 0;
+    rc = stage_matrix<T>(h, a, true, rows, cols, ld, layout, &A, &ldA);
+    if (rc)
+        return rc;
+    rc = run_dense<T>(h, A, ldA, plan, stats);
+    if (rc)
+        return rc;
+    CU(h->out64.ensure(rows * sizeof(long long)));
+    k_widen_i32<<<grid_for(h, rows, 256), 256, 0, h->stream>>>(h->row2col.as<int>(), h->out64.as<long long>(), rows);
+    h->launches++;
+    CU(cudaMemcpyAsync(row_to_col, h->out64.p, rows * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+    if (prices_out)
+        CU(cudaMemcpyAsync(prices_out, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]);
+        stats->ms_upload = ms;
+        cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
+        stats->ms_download = ms;
+        stats->launches = h->launches;
+    }
+    return B200LSAP_OK;
+}
+
+template <typename T>
+int solve_device(b200lsap_handle* h, const T* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                 const b200lsap_options* opts, int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    int rc = check_shape(h, a, rows, cols, ld, layout);
+    if (rc)
+        return rc;
+    if (!row_to_col_dev)
+        return fail(h, B200LSAP_ERR_ARG, "null row_to_col");
+    CU(cudaSetDevice(h->device));
+    DensePlan plan;
+    rc = make_plan(h, rows, cols, opts, plan);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    h->launches = 0;
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    const T* A = nullptr;
+    int64_t ldA = 0;
+    rc = stage_matrix<T>(h, a, false, rows, cols, ld, layout, &A, &ldA);
+    if (rc)
+        return rc;
+    rc = run_dense<T>(h, A, ldA, plan, stats);
+    if (rc)
+        return rc;
+    CU(cudaMemcpyAsync(row_to_col_dev, h->row2col.p, rows * sizeof(int32_t), cudaMemcpyDeviceToDevice, h->stream));
+    if (prices_dev)
+        CU(cudaMemcpyAsync(prices_dev, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]);
+        stats->ms_upload = ms;
+        cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
+        stats->ms_download = ms;
+        stats->launches = h->launches;
+    }
+    return B200LSAP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int b200lsap_solve_f32(b200lsap_handle* h, const float* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                       const b200lsap_options* opts, int64_t* row_to_col, double* prices_out, b200lsap_stats* stats)
+{
+    return solve_host<float>(h, a, rows, cols, ld, layout, opts, row_to_col, prices_out, stats);
+}
+
+int b200lsap_solve_f64(b200lsap_handle* h, const double* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                       const b200lsap_options* opts, int64_t* row_to_col, double* prices_out, b200lsap_stats* stats)
+{
+    return solve_host<double>(h, a, rows, cols, ld, layout, opts, row_to_col, prices_out, stats);
+}
+
+int b200lsap_solve_device_f32(b200lsap_handle* h, const float* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                              const b200lsap_options* opts, int32_t* r2c, double* prices, b200lsap_stats* stats)
+{
+    return solve_device<float>(h, a, rows, cols, ld, layout, opts, r2c, prices, stats);
+}
+
+int b200lsap_solve_device_f64(b200lsap_handle* h, const double* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                              const b200lsap_options* opts, int32_t* r2c, double* prices, b200lsap_stats* stats)
+{
+    return solve_device<double>(h, a, rows, cols, ld, layout, opts, r2c, prices, stats);
+}
+
+} // extern "C"
+
+// =============================================================================================
+// Batched small problems, generators, measurement sweep
+// =============================================================================================
+namespace
+{
+
+int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, int rows, int cols,
+              const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats)
+{
+    b200lsap_options o;
+    b200lsap_options_default(&o);
+    if (opts)
+        o = *opts;
+    if (!(o.eps_multiplier > 0))
+        return fail(h, B200LSAP_ERR_ARG, "eps_multiplier must be positive");
+    BatchParams P;
+    P.a = a_dev_row_major;
+    P.row2col = r2c_dev;
+    P.batch = batch;
+    P.rows = rows;
+    P.cols = cols;
+    P.eps = o.eps_multiplier / (double)cols;
+    P.max_bids = o.max_rounds > 0 ? (int)(o.max_rounds > 0x7fffffff ? 0x7fffffff : o.max_rounds) : 1000000;
+    CU(h->ctrl.ensure(sizeof(DenseCtrl)));
+    P.status = &h->ctrl.as<DenseCtrl>()->status;
+    CU(cudaMemsetAsync(P.status, 0, sizeof(int), h->stream));
+    const int n_pad = (rows * cols + 3) & ~3;
+    const size_t smem = (size_t)kBatchWarps * n_pad * sizeof(float);
+    CU(cudaFuncSetAttribute(k_auction_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_auction_batch, kBatchWarps * 32, smem));
+    if (per_sm < 1)
+        return fail(h, B200LSAP_ERR_SHAPE, "batched problem does not fit in shared memory");
+    int64_t grid = (batch + kBatchWarps - 1) / kBatchWarps;
+    const int64_t resident = (int64_t)per_sm * h->num_sms;
+    if (grid > resident)
+        grid = resident;
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_auction_batch<<<(int)grid, kBatchWarps * 32, smem, h->stream>>>(P);
+    h->launches++;
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaMemcpyAsync(&h->h_ctrl->status, P.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+        stats->ms_solve = ms;
+        stats->eps_final = P.eps;
+        stats->bid_bytes = batch * ((int64_t)rows * cols * 4 + rows * 4);
+        stats->launches = h->launches;
+    }
+    if (h->h_ctrl->status != 0)
+        return fail(h, h->h_ctrl->status, b200lsap_status_string(h->h_ctrl->status));
+    return B200LSAP_OK;
+}
+
+int check_batch(b200lsap_handle* h, const void* a, int64_t batch, int rows, int cols, int layout, const void* out)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (!a || !out)
+        return fail(h, B200LSAP_ERR_ARG, "null pointer");
+    if (layout != B200LSAP_COL_MAJOR && layout != B200LSAP_ROW_MAJOR)
+        return fail(h, B200LSAP_ERR_ARG, "layout must be 0 or 1");
+    if (batch < 0 || rows < 1 || cols < 1 || rows > cols || rows > kBatchMaxRows || cols > kBatchMaxCols)
+        return fail(h, B200LSAP_ERR_SHAPE, "batched mode needs 1 <= rows <= cols, rows <= 32, cols <= 64");
+    return B200LSAP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int b200lsap_solve_batch_device_f32(b200lsap_handle* h, const float* a_dev, int64_t batch, int32_t rows, int32_t cols,
+                                    int layout, const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats)
+{
+    int rc = check_batch(h, a_dev, batch, rows, cols, layout, r2c_dev);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    if (batch == 0)
+        return B200LSAP_OK;
+    CU(cudaSetDevice(h->device));
+    h->launches = 0;
+    const float* src = a_dev;
+    if (layout == B200LSAP_COL_MAJOR && rows > 1 && cols > 1)
+    {
+        const int64_t total = batch * rows * cols;
+        CU(h->batch_in.ensure(total * sizeof(float)));
+        k_batch_to_row_major<<<grid_for(h, total, 256 * 4), 256, 0, h->stream>>>(a_dev, h->batch_in.as<float>(), batch,
+                                                                                rows, cols);
+        h->launches++;
+        src = h->batch_in.as<float>();
+    }
+    return run_batch(h, src, batch, rows, cols, opts, r2c_dev, stats);
+}
+
+int b200lsap_solve_batch_f32(b200lsap_handle* h, const float* a, int64_t batch, int32_t rows, int32_t cols, int layout,
+                             const b200lsap_options* opts, int32_t* row_to_col, b200lsap_stats* stats)
+{
+    int rc = check_batch(h, a, batch, rows, cols, layout, row_to_col);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    if (batch == 0)
+        return B200LSAP_OK;
+    CU(cudaSetDevice(h->device));
+    h->launches = 0;
+    const int64_t total = batch * rows * cols;
+    CU(h->staging.ensure(total * sizeof(float)));
+    CU(h->batch_out.ensure(batch * rows * sizeof(int32_t)));
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    CU(cudaMemcpyAsync(h->staging.p, a, total * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    const float* src = h->staging.as<float>();
+    if (layout == B200LSAP_COL_MAJOR && rows > 1 && cols > 1)
+    {
+        CU(h->batch_in.ensure(total * sizeof(float)));
+        k_batch_to_row_major<<<grid_for(h, total, 256 * 4), 256, 0, h->stream>>>(src, h->batch_in.as<float>(), batch,
+                                                                                rows, cols);
+        h->launches++;
+        src = h->batch_in.as<float>();
+    }
+    rc = run_batch(h, src, batch, rows, cols, opts, h->batch_out.as<int32_t>(), stats);
+    if (rc)
+        return rc;
+    CU(cudaMemcpyAsync(row_to_col, h->batch_out.p, batch * rows * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                       h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]);
+        stats->ms_upload = ms;
+        cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
+        stats->ms_download = ms;
+    }
+    return B200LSAP_OK;
+}
+
+int b200lsap_generate_device_f32(b200lsap_handle* h, float* a_dev, int64_t batch, int64_t rows, int64_t cols,
+                                 int64_t ld, int layout, uint64_t seed, uint64_t problem0)
+{
+    if (!h || !a_dev || batch < 1 || rows < 1 || cols < 1 || ld < (layout ? cols : rows))
+        return fail(h, B200LSAP_ERR_ARG, "bad generate arguments");
+    CU(cudaSetDevice(h->device));
+    const int64_t total = batch * ld * (layout ? rows : cols);
+    k_generate_f32<<<grid_for(h, total, 256 * 4), 256, 0, h->stream>>>(a_dev, batch, rows, cols, ld, layout, seed,
+                                                                       problem0, 0, cols);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(h->stream));
+    return B200LSAP_OK;
+}
+
+int b200lsap_generate_shard_device_f32(b200lsap_handle* h, float* a_dev, int64_t rows, int64_t cols_local, int64_t ld,
+                                       int64_t col0, int64_t cols_global, uint64_t seed, uint64_t problem)
+{
+    if (!h || !a_dev || rows < 1 || cols_local < 1 || ld < cols_local || col0 < 0 || col0 + cols_local > cols_global)
+        return fail(h, B200LSAP_ERR_ARG, "bad generate arguments");
+    CU(cudaSetDevice(h->device));
+    const int64_t total = ld * rows;
+    k_generate_f32<<<grid_for(h, total, 256 * 4), 256, 0, h->stream>>>(a_dev, 1, rows, cols_local, ld,
+                                                                       B200LSAP_ROW_MAJOR, seed, problem, col0,
+                                                                       cols_global);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(h->stream));
+    return B200LSAP_OK;
+}
+
+int b200lsap_bid_sweep_device_f32(b200lsap_handle* h, const float* a_dev, int64_t rows, int64_t cols, int64_t ld,
+                                  int use_last_prices, double* ms_out, int64_t* bytes_out)
+{
+    int rc = check_shape(h, a_dev, rows, cols, ld, B200LSAP_ROW_MAJOR);
+    if (rc)
+        return rc;
+    if (ld % 4 != 0 || cols % 4 != 0 || ((uintptr_t)a_dev & 15) != 0)
+        return fail(h, B200LSAP_ERR_ARG, "bid sweep needs a 16-byte aligned row-major matrix with cols, ld % 4 == 0");
+    CU(cudaSetDevice(h->device));
+    int grid = 0;
+    rc = persistent_grid<float>(h, grid);
+    if (rc)
+        return rc;
+    const bool keep = use_last_prices && h->last_cols == cols;
+    rc = alloc_state<float>(h, rows, cols, ld, grid * kWarpsPerBlock);
+    if (rc)
+        return rc;
+    DenseState<float> s = bind_state<float>(h, a_dev, rows, cols, ld);
+    s.dry = 1;
+    k_init<float><<<grid, kThreads, 0, h->stream>>>(s, keep ? 1 : 0);
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_bid<float><<<grid, kThreads, 0, h->stream>>>(s, 0, (int)rows, 1e-5 / (double)cols);
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+    if (ms_out)
+        *ms_out = ms;
+    if (bytes_out)
+        *bytes_out = rows * cols * (int64_t)sizeof(float);
+    return B200LSAP_OK;
+}
+
+} // extern "C"

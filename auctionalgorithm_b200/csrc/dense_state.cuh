@@ -1,0 +1,130 @@
+// dense_state.cuh — device-side state of one dense auction and the layout kernels.
+//
+// HBM layout: the benefit matrix is held ROW-major, A[i*ld + j], ld a multiple of
+// 32 elements, columns [cols, ld) zero-filled.  A zero is the reference's "no edge" value
+// (Auction.h:134), so the padding is skipped by the same test that skips real zeros and the
+// scan loops need no column tail.  Eigen's default column-major input is
+// transposed once on upload.
+#pragma once
+
+#include "common.cuh"
+#include "../../include/b200lsap_gen.h"
+
+namespace b200lsap
+{
+
+constexpr int kMaxPhases = 48;
+
+// Controller block, one per solve, in device memory (mirrored to pinned host memory at the end).
+struct DenseCtrl
+{
+    int count[2];      // bidders in list[0] / list[1]
+    int status;        // b200lsap_status raised on the device
+    int phase;         // current eps phase
+    int n_phases;
+    int pad0;
+    long long rounds;
+    long long bids;
+    long long max_rounds;
+    double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
+};
+
+template <typename T> struct DenseState
+{
+    const T* A;
+    long long ld;
+    int rows;
+    int cols;
+    int cols4; // cols rounded up to 4 (<= ld): scan bound, padding is zero
+    double* prices;
+    double* profits;
+    BidSlot* slots;  // [cols]
+    int* owner;      // [cols] row holding the column, -1 free
+    int* row2col;    // [rows] column held by the row, -1 unassigned
+    int* bid_col;    // [rows] column the row bid for this round
+    double* bid_val; // [rows] its bid
+    int* list[2];    // compacted unassigned rows, double buffered
+    Top2<T>* partial; // [capacity >= total warps] split-row partial results
+    int* arrive;     // [rows] split-row arrival counters (zero between rounds)
+    DenseCtrl* ctrl;
+    int min_seg;     // smallest row segment a warp takes when rows are split (multiple of 128)
+    int dry;         // 1: measurement sweep, bids are computed and stored but not offered
+};
+
+// ---------------------------------------------------------------------------------------------
+// Column-major [rows x cols] (ld_in) -> row-major (ld_out), zero padding columns [cols, ld_out).
+// 32x32 tiles through shared memory, both sides coalesced.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) k_transpose_pad(const T* __restrict__ in, long long ld_in, T* __restrict__ out,
+                                                       long long ld_out, int rows, int cols)
+{
+    __shared__ T tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5; // 32 x 8
+    const long long tiles_r = (rows + 31) / 32;
+    const long long tiles_c = (ld_out + 31) / 32;
+    for (long long tix = blockIdx.x; tix < tiles_r * tiles_c; tix += gridDim.x)
+    {
+        const int r0 = (int)(tix % tiles_r) * 32, c0 = (int)(tix / tiles_r) * 32;
+#pragma unroll
+        for (int k = 0; k < 32; k += 8)
+        {
+            const int c = c0 + ty + k, r = r0 + tx;
+            tile[ty + k][tx] = (c < cols && r < rows) ? in[(long long)c * ld_in + r] : T(0);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 32; k += 8)
+        {
+            const int r = r0 + ty + k, c = c0 + tx;
+            if (r < rows && c < ld_out)
+                out[(long long)r * ld_out + c] = tile[tx][ty + k];
+        }
+        __syncthreads();
+    }
+}
+
+// Row-major with an arbitrary ld_in -> padded row-major.
+template <typename T>
+__global__ void __launch_bounds__(256) k_copy_pad(const T* __restrict__ in, long long ld_in, T* __restrict__ out,
+                                                  long long ld_out, int rows, int cols)
+{
+    const long long total = (long long)rows * ld_out;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x)
+    {
+        const long long r = e / ld_out;
+        const int c = (int)(e - r * ld_out);
+        out[e] = c < cols ? in[r * ld_in + c] : T(0);
+    }
+}
+
+// Synthetic inputs, bit-identical to oracle_generate_f32 (include/b200lsap_gen.h).
+// Element (b, i, j) of a batch; col0/cols_global select a column shard of one big problem.
+__global__ void __launch_bounds__(256) k_generate_f32(float* __restrict__ out, long long batch, long long rows,
+                                                      long long cols, long long ld, int layout,
+                                                      unsigned long long seed, unsigned long long problem0,
+                                                      long long col0, long long cols_global)
+{
+    const long long minor = layout ? cols : rows;
+    const long long major = layout ? rows : cols;
+    const long long per_problem = ld * major;
+    const long long total = batch * per_problem;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x)
+    {
+        const long long b = e / per_problem;
+        const long long r = e - b * per_problem;
+        const long long mj = r / ld, mn = r - mj * ld;
+        float v = 0.f;
+        if (mn < minor)
+        {
+            const long long i = layout ? mj : mn, j = layout ? mn : mj;
+            const uint64_t key = b200lsap_gen_key(seed, problem0 + (unsigned long long)b);
+            v = b200lsap_gen_value(key, (uint64_t)(i * cols_global + col0 + j));
+        }
+        out[e] = v;
+    }
+}
+
+} // namespace b200lsap

@@ -1,0 +1,208 @@
+"""Host-side mirror of the reference's solver interface over the C-ABI (include/b200lsap.h).
+
+Reference interface mirrored (relative to /root/reference/AuctionAlgorithm/):
+    LSAP::Auction<Scalar, MatrixType>::solve(const MatrixType& a) -> Edges          Auction.h:44
+    LSAP::AuctionMT<Scalar, MatrixType>::solve(const MatrixType& m, noOfThreads=2)  AuctionMT.h:50
+    Edge{size_t x; size_t y; Scalar v;}, Edges = std::vector<Edge>                  AuctionCommon.h:30-40
+
+Same names, same argument meaning: a dense rows x cols benefit matrix with rows <= cols and
+coefficients in [0, 1] where 0 means "no edge"; the result is one edge per row.  Edges come
+back sorted by row (the reference's order is the order in which columns were first won,
+which a synchronous parallel auction does not reproduce; SURVEY.md §7 hard part 1).
+Where the reference never returns (rows > cols, an all-zero row) B200LsapError is raised.
+
+The C++ spelling of the same mirror is include/AuctionB200.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _capi
+from ._capi import B200LsapError, Options, Stats
+
+EDGE_DTYPE_F64 = np.dtype([("x", np.uint64), ("y", np.uint64), ("v", np.float64)])  # sizeof(Edge) == 24
+EDGE_DTYPE_F32 = np.dtype([("x", np.uint64), ("y", np.uint64), ("v", np.float32)], align=True)
+
+
+class Handle:
+    """Owns a b200lsap_handle (device buffers + stream).  One per host thread."""
+
+    def __init__(self, device: int = -1):
+        self._lib = _capi.lib()
+        self._h = C.c_void_p()
+        rc = self._lib.b200lsap_create(C.byref(self._h), device)
+        if rc != _capi.OK:
+            raise B200LsapError(rc, self._lib.b200lsap_status_string(rc).decode())
+        self.last_stats: Optional[dict] = None
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.b200lsap_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -------------------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != _capi.OK:
+            raise B200LsapError(rc, self._lib.b200lsap_last_error(self._h).decode())
+
+    @staticmethod
+    def _opts(eps_multiplier=None, eps_scaling=None, eps_start=None, eps_factor=None, max_rounds=None,
+              driver=None) -> Options:
+        o = Options()
+        _capi.lib().b200lsap_options_default(C.byref(o))
+        if eps_multiplier is not None:
+            o.eps_multiplier = eps_multiplier
+        if eps_scaling is not None:
+            o.eps_scaling = {True: 1, False: 0}.get(eps_scaling, eps_scaling)
+        if eps_start is not None:
+            o.eps_start = eps_start
+        if eps_factor is not None:
+            o.eps_factor = eps_factor
+        if max_rounds is not None:
+            o.max_rounds = max_rounds
+        if driver is not None:
+            o.driver = driver
+        return o
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self._lib.b200lsap_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def solve(self, a: np.ndarray, want_prices: bool = False, **options):
+        """Host matrix in, row_to_col (int64[rows]) out.  float32 or float64, C or F order."""
+        if a.ndim != 2:
+            raise ValueError("need a 2-D matrix")
+        if a.dtype not in (np.float32, np.float64):
+            raise TypeError("use real types as coefficients (Auction.h:40): float32 or float64")
+        if a.flags.c_contiguous:
+            layout, ld = _capi.ROW_MAJOR, a.shape[1]
+        elif a.flags.f_contiguous:
+            layout, ld = _capi.COL_MAJOR, a.shape[0]
+        else:
+            a = np.ascontiguousarray(a)
+            layout, ld = _capi.ROW_MAJOR, a.shape[1]
+        rows, cols = a.shape
+        r2c = np.full(max(rows, 1), -1, np.int64)
+        prices = np.zeros(max(cols, 1), np.float64) if want_prices else None
+        st = Stats()
+        o = self._opts(**options)
+        fn = self._lib.b200lsap_solve_f32 if a.dtype == np.float32 else self._lib.b200lsap_solve_f64
+        rc = fn(self._h, a.ctypes.data, rows, cols, ld, layout, C.byref(o), r2c.ctypes.data,
+                prices.ctypes.data if want_prices else None, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return (r2c[:rows], prices) if want_prices else r2c[:rows]
+
+    def solve_device(self, a_ptr: int, rows: int, cols: int, ld: int, layout: int, r2c_ptr: int,
+                     prices_ptr: int = 0, dtype=np.float32, **options) -> dict:
+        st = Stats()
+        o = self._opts(**options)
+        fn = self._lib.b200lsap_solve_device_f32 if dtype == np.float32 else self._lib.b200lsap_solve_device_f64
+        rc = fn(self._h, C.c_void_p(a_ptr), rows, cols, ld, layout, C.byref(o), C.c_void_p(r2c_ptr),
+                C.c_void_p(prices_ptr) if prices_ptr else None, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return self.last_stats
+
+    def solve_batch(self, a: np.ndarray, layout: int = _capi.ROW_MAJOR, **options) -> np.ndarray:
+        """a: [batch, rows, cols] float32 (layout ROW_MAJOR) or [batch, cols, rows] memory
+        order (COL_MAJOR, pass the array as [batch, rows, cols] logical shape with
+        layout=COL_MAJOR and C-contiguous storage of the transposed problems)."""
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        batch, rows, cols = a.shape
+        out = np.full((batch, rows), -1, np.int32)
+        st = Stats()
+        o = self._opts(**options)
+        rc = self._lib.b200lsap_solve_batch_f32(self._h, a.ctypes.data, batch, rows, cols, layout, C.byref(o),
+                                                out.ctypes.data, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return out
+
+    def solve_batch_device(self, a_ptr: int, batch: int, rows: int, cols: int, r2c_ptr: int,
+                           layout: int = _capi.ROW_MAJOR, **options) -> dict:
+        st = Stats()
+        o = self._opts(**options)
+        rc = self._lib.b200lsap_solve_batch_device_f32(self._h, C.c_void_p(a_ptr), batch, rows, cols, layout,
+                                                       C.byref(o), C.c_void_p(r2c_ptr), C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return self.last_stats
+
+    def generate_device(self, a_ptr: int, batch: int, rows: int, cols: int, ld: int, layout: int, seed: int,
+                        problem0: int = 0):
+        self._check(self._lib.b200lsap_generate_device_f32(self._h, C.c_void_p(a_ptr), batch, rows, cols, ld,
+                                                           layout, seed, problem0))
+
+    def generate_shard_device(self, a_ptr: int, rows: int, cols_local: int, ld: int, col0: int, cols_global: int,
+                              seed: int, problem: int = 0):
+        self._check(self._lib.b200lsap_generate_shard_device_f32(self._h, C.c_void_p(a_ptr), rows, cols_local, ld,
+                                                                 col0, cols_global, seed, problem))
+
+    def bid_sweep_device(self, a_ptr: int, rows: int, cols: int, ld: int, use_last_prices: bool = True):
+        ms = C.c_double(0)
+        nbytes = C.c_int64(0)
+        self._check(self._lib.b200lsap_bid_sweep_device_f32(self._h, C.c_void_p(a_ptr), rows, cols, ld,
+                                                            int(use_last_prices), C.byref(ms), C.byref(nbytes)))
+        return ms.value, nbytes.value
+
+
+_default_handle: Optional[Handle] = None
+
+
+def default_handle() -> Handle:
+    global _default_handle
+    if _default_handle is None:
+        _default_handle = Handle()
+    return _default_handle
+
+
+def edges_from_assignment(a: np.ndarray, row_to_col: np.ndarray) -> np.ndarray:
+    """Edge{x, y, v = a(x, y)} per row, v taken from the caller's matrix (Auction.h:273,283)."""
+    dt = EDGE_DTYPE_F64 if a.dtype == np.float64 else EDGE_DTYPE_F32
+    e = np.empty(len(row_to_col), dt)
+    e["x"] = np.arange(len(row_to_col), dtype=np.uint64)
+    e["y"] = row_to_col.astype(np.uint64)
+    e["v"] = a[np.arange(len(row_to_col)), row_to_col]
+    return e
+
+
+class Auction:
+    """LSAP::Auction<Scalar, MatrixType> (Auction.h:19-44): `Auction.solve(a)` -> Edges."""
+
+    @staticmethod
+    def solve(a: np.ndarray, handle: Optional[Handle] = None, **options) -> np.ndarray:
+        h = handle or default_handle()
+        r2c = h.solve(a, **options)
+        return edges_from_assignment(a, r2c)
+
+
+class AuctionMT:
+    """LSAP::AuctionMT<Scalar, MatrixType> (AuctionMT.h:24-50).  noOfThreads is accepted for
+    source compatibility and ignored: the column-interval split it controlled
+    (AuctionMT.h:76-77) is done by the GPU grid.  Unlike the reference it is also correct for
+    rows < cols."""
+
+    @staticmethod
+    def solve(m: np.ndarray, noOfThreads: int = 2, handle: Optional[Handle] = None, **options) -> np.ndarray:
+        del noOfThreads
+        return Auction.solve(m, handle=handle, **options)
+
+
+def objective(edges: np.ndarray) -> float:
+    """objFuncValue of the reference's driver (LSAP.cpp:12-19), summed in double."""
+    return float(np.sum(edges["v"].astype(np.float64)))

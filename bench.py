@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 auction path (contract: task brief §④).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c2|c3]
+
+Default workload (N = 1): BASELINE.json configs[3] = C4, one dense 16384 x 16384 fp32 problem
+(1 GiB, larger than L2) solved to the reference's assignment.  A step = one full solve.
+  value      solve ms per problem, matrix already resident in HBM (CUDA events on the stream)
+  e2e        the same solve through the reference-facing host API (Eigen-layout column-major
+             pinned host matrix in, row->column out): H2D + transpose + solve + D2H in the timed region
+  roofline   the bidding kernel alone (every row bids once, one launch), measured live
+  cpu_baseline  the CPU oracle port of Auction<double>::solve on a bounded sample of the same input
+  mht        BASELINE's second quantity: batched 32x48 problems/s (C3), sharded over the N GPUs
+N > 1: the dense solve does not shard ("replicas only"): every rank solves its own
+replica and value is the aggregate ms per solve (step time / N); the batched C3 numbers in `mht`
+are the path that shards.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "c1": dict(rows=200, cols=300), "c2": dict(rows=2048, cols=3072), "c4": dict(rows=16384, cols=16384),
+}
+SEED = 1
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks() -> tuple[float, str]:
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def c4_reference_counters() -> dict:
+    p = os.path.join(ROOT, "tests", "golden", "c4_oracle_stats.json")
+    return json.load(open(p)) if os.path.exists(p) else {}
+
+
+def cpu_sample(rows: int, cols: int, seconds_target: float = 12.0) -> dict:
+    """Times the CPU oracle port (oracle/auction_oracle.c = Auction<double>::solve restated, pinned
+    bit-for-bit against the compiled reference) on a bounded sample of the workload and scales it
+    to a whole solve.  Small workloads run to completion; C4 runs a bid budget and is scaled by the
+    reference's total bid count recorded in tests/golden/c4_oracle_stats.json."""
+    import numpy as np
+    from oracle import pyoracle as po
+    po.build()
+    a = np.asfortranarray(po.generate(rows, cols, SEED).astype(np.float64))  # Eigen layout, widened fp32
+    full = rows * cols <= 4096 * 6144 and rows != cols
+    if full:
+        t = time.perf_counter()
+        out = po.oracle_solve(a)
+        sec = time.perf_counter() - t
+        return dict(value=sec * 1e3, unit="ms", cores=1, kind="port",
+                    sample=f"full Auction<double> solve of {rows}x{cols} seed {SEED}: {out['stats']['bids']} bids")
+    probe = po.oracle_solve(a, max_bids=2000)
+    t = time.perf_counter()
+    probe = po.oracle_solve(a, max_bids=4000)
+    per_bid = (time.perf_counter() - t) / max(probe["stats"]["bids"], 1)
+    budget = max(4000, int(seconds_target / per_bid))
+    t = time.perf_counter()
+    out = po.oracle_solve(a, max_bids=budget)
+    sec = time.perf_counter() - t
+    bids = out["stats"]["bids"]
+    ref = c4_reference_counters() if (rows, cols) == (16384, 16384) else {}
+    if out["status"] == po.ORC_OK:
+        return dict(value=sec * 1e3, unit="ms", cores=1, kind="port", sample=f"full solve, {bids} bids")
+    if ref.get("bids"):
+        total = ref["bids"]
+        note = (f"first {bids} bids of Auction<double> on {rows}x{cols} seed {SEED} took {sec:.1f} s "
+                f"({1e6 * sec / bids:.0f} us/bid); scaled to the {total} bids of the full reference solve "
+                f"(measured offline: {ref.get('seconds_reference', 0):.0f} s, tests/golden/c4_oracle_stats.json)")
+        return dict(value=sec / bids * total * 1e3, unit="ms", cores=1, kind="port", sample=note)
+    return dict(value=None, unit="ms", cores=1, kind="port",
+                sample=f"first {bids} bids took {sec:.1f} s ({1e6 * sec / bids:.0f} us/bid); total bid count unknown")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    vals, last = [], None
+    for k in range(args.warmup + args.steps):
+        last = cpu_sample(w["rows"], w["cols"], seconds_target=8.0)
+        if k >= args.warmup and last["value"] is not None:
+            vals.append(last["value"])
+    v = statistics.mean(vals) if vals else None
+    last["value"] = v
+    print(json.dumps({
+        "impl": "reference", "metric": f"solve_ms_{w['rows']}x{w['cols']}_fp32", "value": v, "unit": "ms",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": v,
+        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: dense {w['rows']}x{w['cols']} fp32 widened to f64, seed {SEED}, "
+                               "reference Auction<double>::solve on the host, single thread"},
+        "cpu_baseline": last,
+        "e2e": {"value": v, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int):
+    """C3: this rank's shard of the batch, generated on the device (inputs resident in HBM)."""
+    t = torch.empty((n_problems, 32, 48), dtype=torch.float32, device="cuda")
+    out = torch.empty((n_problems, 32), dtype=torch.int32, device="cuda")
+    handle.generate_device(t.data_ptr(), n_problems, 32, 48, 48, 1, SEED, problem0=rank * n_problems)
+    for _ in range(warmup):
+        handle.solve_batch_device(t.data_ptr(), n_problems, 32, 48, out.data_ptr())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        st = handle.solve_batch_device(t.data_ptr(), n_problems, 32, 48, out.data_ptr())
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    del t, out
+    return ms, st["bid_bytes"]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--mht-problems", type=int, default=1 << 20, help="C3 problems per GPU")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from auctionalgorithm_b200 import build
+    build.build()
+    import auctionalgorithm_b200 as ab
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    w = WORKLOADS[args.workload]
+    rows, cols = w["rows"], w["cols"]
+    handle = ab.Handle(local)
+    handle.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident solve --------------------------------------------------------------
+    a_dev = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+    r2c_dev = torch.empty(rows, dtype=torch.int32, device="cuda")
+    handle.generate_device(a_dev.data_ptr(), 1, rows, cols, cols, ab.ROW_MAJOR, SEED)
+    for _ in range(args.warmup):
+        handle.solve_device(a_dev.data_ptr(), rows, cols, cols, ab.ROW_MAJOR, r2c_dev.data_ptr())
+    sampler = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    e0.record()
+    launches = 0
+    for _ in range(args.steps):
+        st = handle.solve_device(a_dev.data_ptr(), rows, cols, cols, ab.ROW_MAJOR, r2c_dev.data_ptr())
+        launches += st["launches"]
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        tt = torch.tensor([ms_step], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step = float(tt.item())
+    solve_stats = st
+
+    # ---- parity of what was just timed (rank 0, against the reference-made golden vector) ------
+    parity_note = None
+    gpath = os.path.join(ROOT, "tests", "golden", f"auction_{rows}x{cols}_s{SEED}.npz")
+    if rank == 0 and os.path.exists(gpath):
+        g = np.load(gpath)
+        ref = np.full(rows, -1, np.int64)
+        ref[g["x"]] = g["y"]
+        parity_note = "exact" if np.array_equal(r2c_dev.cpu().numpy(), ref) else "differs-from-golden"
+
+    # ---- bidding kernel alone: the roofline ---------------------------------------------------
+    sweep_ms = []
+    for _ in range(3 + 5):
+        ms, nbytes = handle.bid_sweep_device(a_dev.data_ptr(), rows, cols, cols, use_last_prices=True)
+        sweep_ms.append(ms)
+    sweep = statistics.mean(sweep_ms[3:])
+    peak, peak_src = peaks()
+    roofline = {"bound": "hbm", "kernel": "k_bid<float> (bidding phase, every row bids once)",
+                "achieved": nbytes / sweep / 1e6, "peak": peak, "unit": "GB/s",
+                "frac": nbytes / sweep / 1e6 / peak, "traffic": None, "peak_source": peak_src,
+                "ms_per_launch": sweep, "algorithmic_bytes_per_launch": nbytes}
+    solve_gbs = solve_stats["bid_bytes"] / (ms_step * 1e6)
+
+    # ---- end to end through the host API --------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((cols, rows), dtype=torch.float32).pin_memory()   # column-major storage (Eigen)
+        host.copy_(a_dev.t())
+        a_host = host.numpy().T                                             # F-contiguous rows x cols view
+        del a_dev
+        for _ in range(max(1, min(args.warmup, 2))):
+            handle.solve(a_host)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            r2c_host = handle.solve(a_host)
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        if world > 1:
+            tt = torch.tensor([e2e_ms], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            e2e_ms = float(tt.item())
+        e2e = {"value": e2e_ms / world, "unit": "ms", "h2d_bytes_per_step": rows * cols * 4,
+               "d2h_bytes_per_step": rows * 8, "ms_upload": handle.last_stats["ms_upload"],
+               "ms_solve": handle.last_stats["ms_solve"], "ms_download": handle.last_stats["ms_download"],
+               "input": "pinned host, column-major (Eigen default)"}
+        launches_e2e = handle.last_stats["launches"]
+        del host, a_host
+    else:
+        del a_dev
+    torch.cuda.empty_cache()
+
+    # ---- C3: batched 32x48 problems, sharded over ranks, no collective -------------------------
+    mht_ms, mht_bytes = run_mht(handle, torch, args.mht_problems, rank, max(args.steps, 3), 3)
+    if world > 1:
+        tt = torch.tensor([mht_ms], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        mht_ms = float(tt.item())
+    mht = {"problems_per_s": args.mht_problems * world / (mht_ms * 1e-3), "problems": args.mht_problems * world,
+           "ms_per_step": mht_ms, "gbs_per_gpu": mht_bytes / mht_ms / 1e6, "frac_of_hbm_peak": mht_bytes / mht_ms / 1e6 / peak,
+           "layout": "row-major 32x48 fp32 problems, device-generated, resident in HBM"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_sample(rows, cols)
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": f"solve_ms_{rows}x{cols}_fp32", "value": ms_step / world, "unit": "ms", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: dense {rows}x{cols} fp32 (BASELINE.json configs), uniform grid "
+                                   f"(0,1], seed {SEED}, device-generated; inputs larger than L2" if rows * cols * 4 > 126e6
+                       else f"{args.workload}: dense {rows}x{cols} fp32, seed {SEED} (L2-resident)",
+                       "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (dense solve does not shard)",
+                       "eps_final": solve_stats["eps_final"], "rounds": solve_stats["rounds"], "bids": solve_stats["bids"],
+                       "phases": solve_stats["phases"], "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"], 1),
+                       "parity_vs_reference_golden": parity_note},
+            "roofline": roofline,
+            "solve_algorithmic_gbs": solve_gbs,
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "mht": mht,
+            "gpu_launches": launches,
+            "clocks": clocks,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,159 @@
+/*
+ * b200lsap.h — C-ABI of the B200-native auction solver (libb200lsap.so).
+ *
+ * This is the drop-in boundary for the reference's dense solve path.  Every entry point
+ * names the reference interface it replaces, relative to /root/reference/:
+ *
+ *   b200lsap_solve_f64 / _f32      LSAP::Auction<Scalar,MatrixType>::solve(const MatrixType&)
+ *                                  AuctionAlgorithm/Auction.h:44-109 (controller),
+ *                                  :124-152 findForward, :210-306 forward; and
+ *                                  LSAP::AuctionMT<Scalar,MatrixType>::solve(m, noOfThreads)
+ *                                  AuctionAlgorithm/AuctionMT.h:50-171, :335-451 parallelForward,
+ *                                  AuctionAlgorithm/AuctionCommon.h:86-129 forwardGS
+ *   b200lsap_solve_batch_f32       the same solve() called once per problem by the caller
+ *                                  (the reference has no batch API; LSAP.cpp:44 is one call)
+ *   b200lsap_*_device_*            same operations on matrices already resident in HBM
+ *   b200lsap_options.eps_multiplier  __AUCTION_EPSILON_MULTIPLIER, internal.h:16
+ *   B200LSAP_NO_SECOND_BEST          __AUCTION_INF, internal.h:17
+ *   b200lsap_shard_*               AuctionMT's column-interval decomposition
+ *                                  (AuctionMT.h:76-77, AuctionCommon.h:302-320) and the top-2
+ *                                  merge of thread 0 (AuctionMT.h:377-398), across GPUs
+ *
+ * Plain C types only.  The caller owns every host buffer; a handle owns its device buffers
+ * and stream, is reusable, and serves one host thread at a time.  Nothing here falls back
+ * to the CPU: without a CUDA device b200lsap_create fails.
+ *
+ * Semantics kept from the reference: a(i,j) == 0 means "no edge" (Auction.h:134); ties in a
+ * row go to the lowest column (strict '>' at Auction.h:136); the second-best value may equal
+ * the best (Auction.h:147-148); eps = eps_multiplier / cols (Auction.h:55); bid = a - w + eps
+ * evaluated in double (Auction.h:250).  Where the reference never returns (rows > cols, a row
+ * without an edge) these functions return an error status instead.
+ */
+#ifndef B200LSAP_H_
+#define B200LSAP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200LSAP_VERSION 100
+
+#define B200LSAP_COL_MAJOR 0 /* Eigen::Matrix default: a(i,j) = a[i + j*ld] */
+#define B200LSAP_ROW_MAJOR 1 /* a(i,j) = a[i*ld + j] */
+
+#define B200LSAP_NO_SECOND_BEST 1e6 /* internal.h:17 */
+
+typedef enum
+{
+    B200LSAP_OK = 0,
+    B200LSAP_ERR_SHAPE = 1,      /* rows > cols, or a non-positive dimension, or ld too small */
+    B200LSAP_ERR_INFEASIBLE = 2, /* some row has no non-zero coefficient */
+    B200LSAP_ERR_MAX_ROUNDS = 3, /* watchdog: max_rounds auction rounds without termination */
+    B200LSAP_ERR_CUDA = 4,       /* see b200lsap_last_error */
+    B200LSAP_ERR_ARG = 5,        /* null pointer, bad option */
+    B200LSAP_ERR_NO_DEVICE = 6
+} b200lsap_status;
+
+typedef struct b200lsap_handle b200lsap_handle;
+
+typedef struct
+{
+    double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
+    int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on */
+    double eps_start;      /* first eps of the scaling schedule; <= 0: default */
+    double eps_factor;     /* eps is divided by this between phases; <= 1: default */
+    int64_t max_rounds;    /* watchdog; <= 0: default */
+    int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
+                              of a round, driven from the host (profiling and cross-checks) */
+    int32_t reserved;
+} b200lsap_options;
+
+typedef struct
+{
+    int64_t rounds;    /* synchronous auction rounds executed */
+    int64_t bids;      /* sum over rounds of bidding rows */
+    int64_t phases;    /* eps phases (1 without scaling) */
+    int64_t bid_bytes; /* algorithmic bytes of the bidding phase: bids * cols * sizeof(element) */
+    double eps_final;
+    double ms_upload;  /* host->device copy (+ transpose when the input is column-major) */
+    double ms_solve;   /* auction kernels only, CUDA events on the handle's stream */
+    double ms_download;
+    int64_t launches;  /* kernels launched by this call */
+    int64_t reserved[4];
+} b200lsap_stats;
+
+/* device < 0: the current CUDA device.  Creates the handle's own non-blocking stream. */
+int b200lsap_create(b200lsap_handle** handle, int device);
+int b200lsap_destroy(b200lsap_handle* handle);
+/* Run the handle's work on a caller-owned cudaStream_t (e.g. torch's current stream). */
+int b200lsap_set_stream(b200lsap_handle* handle, void* cuda_stream);
+const char* b200lsap_last_error(const b200lsap_handle* handle);
+const char* b200lsap_status_string(int status);
+void b200lsap_options_default(b200lsap_options* opts);
+
+/*
+ * Replaces Auction<Scalar>::solve / AuctionMT<Scalar>::solve on a dense host matrix
+ * (Auction.h:44, AuctionMT.h:50).  a: rows x cols, leading dimension ld, in `layout`.
+ * row_to_col[i] receives the column assigned to row i (always >= 0 on success).  The caller
+ * rebuilds Edge{x=i, y=row_to_col[i], v=a(i,y)} from its own matrix (Auction.h:273,283).
+ * prices_out (nullable): cols doubles, the final object prices.  opts, stats nullable.
+ * The fp32 entry computes a - p in double on the exactly widened coefficients, i.e. it is
+ * Auction<double> on the widened matrix, the instantiation that terminates.
+ */
+int b200lsap_solve_f32(b200lsap_handle* handle, const float* a, int64_t rows, int64_t cols, int64_t ld,
+                       int layout, const b200lsap_options* opts, int64_t* row_to_col, double* prices_out,
+                       b200lsap_stats* stats);
+int b200lsap_solve_f64(b200lsap_handle* handle, const double* a, int64_t rows, int64_t cols, int64_t ld,
+                       int layout, const b200lsap_options* opts, int64_t* row_to_col, double* prices_out,
+                       b200lsap_stats* stats);
+
+/* Same solve on a matrix already in device memory.  ROW_MAJOR with ld % 4 == 0 and a
+ * 16-byte aligned base is used in place; anything else is first re-laid out on the device.
+ * row_to_col_dev: int32[rows] in device memory.  prices_dev nullable (double[cols], device). */
+int b200lsap_solve_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols,
+                              int64_t ld, int layout, const b200lsap_options* opts, int32_t* row_to_col_dev,
+                              double* prices_dev, b200lsap_stats* stats);
+int b200lsap_solve_device_f64(b200lsap_handle* handle, const double* a_dev, int64_t rows, int64_t cols,
+                              int64_t ld, int layout, const b200lsap_options* opts, int32_t* row_to_col_dev,
+                              double* prices_dev, b200lsap_stats* stats);
+
+/*
+ * Batched mode for MHT-style data association: `batch` independent rows x cols problems,
+ * problem b at a + b*rows*cols, each stored in `layout` with ld = its minor dimension.
+ * One warp solves one problem with its matrix held in shared memory.  rows <= cols <= 64.
+ * row_to_col: int32[batch*rows].  Host and device-resident variants.
+ */
+int b200lsap_solve_batch_f32(b200lsap_handle* handle, const float* a, int64_t batch, int32_t rows,
+                             int32_t cols, int layout, const b200lsap_options* opts, int32_t* row_to_col,
+                             b200lsap_stats* stats);
+int b200lsap_solve_batch_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t batch, int32_t rows,
+                                    int32_t cols, int layout, const b200lsap_options* opts,
+                                    int32_t* row_to_col_dev, b200lsap_stats* stats);
+
+/* Synthetic inputs (include/b200lsap_gen.h) written straight into device memory:
+ * `batch` consecutive problems starting at problem id problem0, each rows x cols with leading
+ * dimension ld in `layout`, problem stride = ld * (layout ? rows : cols) elements. */
+int b200lsap_generate_device_f32(b200lsap_handle* handle, float* a_dev, int64_t batch, int64_t rows,
+                                 int64_t cols, int64_t ld, int layout, uint64_t seed, uint64_t problem0);
+/* Column shard of one big problem: fills local columns [0, cols_local) with the values of
+ * global columns [col0, col0+cols_local) of a rows x cols_global matrix. */
+int b200lsap_generate_shard_device_f32(b200lsap_handle* handle, float* a_dev, int64_t rows,
+                                       int64_t cols_local, int64_t ld, int64_t col0, int64_t cols_global,
+                                       uint64_t seed, uint64_t problem);
+
+/* Full-sweep bidding pass for measurement: every row bids once against the handle's current
+ * prices of the last device solve (or zero prices), nothing is updated.  Returns through
+ * ms_out the CUDA-event time of that single kernel; bytes_out = rows*cols*sizeof(float). */
+int b200lsap_bid_sweep_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols,
+                                  int64_t ld, int use_last_prices, double* ms_out, int64_t* bytes_out);
+
+/* Pinned host memory for callers that want full-rate PCIe copies. */
+void* b200lsap_host_alloc(int64_t bytes);
+void b200lsap_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LSAP_H_ */

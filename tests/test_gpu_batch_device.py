@@ -1,0 +1,114 @@
+"""GPU tests of the batched mode (MHT-style 32x48 problems) and of the device-resident entry
+points, through the C-ABI."""
+import numpy as np
+import pytest
+
+import parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _batch_inputs(oracle_lib, batch, rows, cols, seed, problem0=0):
+    return np.stack([oracle_lib.generate(rows, cols, seed, problem=problem0 + b) for b in range(batch)])
+
+
+@pytest.mark.parametrize("name", ["batch_256x32x48_s1.npz", "batch_64x8x12_s1.npz"])
+def test_batch_matches_reference_exactly(handle, oracle_lib, name):
+    # the batched kernel keeps the reference's Gauss-Seidel order: identical assignment, always
+    g = np.load(parity.GOLDEN_DIR + "/" + name)
+    batch, rows, cols, seed = (int(g[k]) for k in ("batch", "rows", "cols", "seed"))
+    a = _batch_inputs(oracle_lib, batch, rows, cols, seed)
+    out = handle.solve_batch(a)
+    assert np.array_equal(out, g["row_to_col"])
+    a_cm = np.ascontiguousarray(a.transpose(0, 2, 1))  # each problem column-major, Eigen's default
+    import auctionalgorithm_b200 as ab
+    out_cm = handle.solve_batch(a_cm.reshape(batch, rows, cols), layout=ab.COL_MAJOR)
+    assert np.array_equal(out_cm, g["row_to_col"])
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (1, 7), (5, 5), (17, 33), (32, 32), (32, 64), (31, 63), (20, 21)])
+def test_batch_shapes_against_oracle(handle, oracle_lib, shape):
+    rows, cols = shape
+    a = _batch_inputs(oracle_lib, 200, rows, cols, 9)
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_batch_with_zeros_and_ties(handle, oracle_lib):
+    a = _batch_inputs(oracle_lib, 300, 16, 24, 4)
+    rng = np.random.default_rng(0)
+    a[rng.random(a.shape) < 0.3] = 0.0
+    a[:, :, :2] = np.maximum(a[:, :, :2], 0.25)       # keep every row feasible
+    a[:50] = np.round(a[:50] * 8) / 8                 # many exact ties
+    a[:50, :, :2] = np.maximum(a[:50, :, :2], 0.125)
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_batch_errors(handle):
+    import auctionalgorithm_b200 as ab
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve_batch(np.ones((2, 33, 40), np.float32))
+    assert e.value.status == ab.ERR_SHAPE
+    a = np.ones((3, 4, 6), np.float32)
+    a[1, 2] = 0
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve_batch(a)
+    assert e.value.status == ab.ERR_INFEASIBLE
+    assert handle.solve_batch(np.ones((0, 4, 6), np.float32)).shape == (0, 4)
+
+
+def test_device_generator_is_bit_identical(handle, oracle_lib):
+    import torch
+    import auctionalgorithm_b200 as ab
+    for batch, rows, cols, ld, layout in [(3, 32, 48, 48, ab.ROW_MAJOR), (1, 100, 130, 160, ab.ROW_MAJOR),
+                                           (2, 20, 30, 20, ab.COL_MAJOR)]:
+        major = rows if layout == ab.ROW_MAJOR else cols
+        minor = cols if layout == ab.ROW_MAJOR else rows
+        t = torch.full((batch, major, ld), -1.0, dtype=torch.float32, device="cuda")
+        handle.generate_device(t.data_ptr(), batch, rows, cols, ld, layout, seed=5, problem0=7)
+        got = t.cpu().numpy()
+        for b in range(batch):
+            want = oracle_lib.generate(rows, cols, 5, problem=7 + b)
+            blk = got[b, :, :minor]
+            assert np.array_equal(blk if layout == ab.ROW_MAJOR else blk.T, want)
+            assert (got[b, :, minor:] == 0).all()
+    # column shard of a bigger problem
+    t = torch.empty((64, 32), dtype=torch.float32, device="cuda")
+    handle.generate_shard_device(t.data_ptr(), 64, 32, 32, col0=40, cols_global=100, seed=3)
+    assert np.array_equal(t.cpu().numpy(), oracle_lib.generate(64, 100, 3)[:, 40:72])
+
+
+def test_device_solve_matches_host_solve(handle, oracle_lib):
+    import torch
+    import auctionalgorithm_b200 as ab
+    for rows, cols in [(200, 300), (256, 256), (123, 457)]:
+        a = oracle_lib.generate(rows, cols, 12)
+        want, wprices = handle.solve(a, want_prices=True)
+        for layout, host in ((ab.ROW_MAJOR, a), (ab.COL_MAJOR, np.asfortranarray(a))):
+            t = torch.from_numpy(np.ascontiguousarray(host if layout == ab.ROW_MAJOR else host.T)).cuda()
+            r2c = torch.empty(rows, dtype=torch.int32, device="cuda")
+            prices = torch.empty(cols, dtype=torch.float64, device="cuda")
+            handle.solve_device(t.data_ptr(), rows, cols, cols if layout == ab.ROW_MAJOR else rows, layout,
+                                r2c.data_ptr(), prices.data_ptr())
+            assert np.array_equal(r2c.cpu().numpy(), want) and np.array_equal(prices.cpu().numpy(), wprices)
+
+
+def test_batch_device_and_stream_handoff(handle, oracle_lib):
+    import torch
+    g = np.load(parity.GOLDEN_DIR + "/batch_256x32x48_s1.npz")
+    t = torch.empty((256, 32, 48), dtype=torch.float32, device="cuda")
+    handle.generate_device(t.data_ptr(), 256, 32, 48, 48, 1, seed=1, problem0=0)
+    out = torch.empty((256, 32), dtype=torch.int32, device="cuda")
+    handle.solve_batch_device(t.data_ptr(), 256, 32, 48, out.data_ptr())
+    assert np.array_equal(out.cpu().numpy(), g["row_to_col"])
+
+
+def test_bid_sweep_reports_bytes(handle, oracle_lib):
+    import torch
+    t = torch.empty((1024, 2048), dtype=torch.float32, device="cuda")
+    handle.generate_device(t.data_ptr(), 1, 1024, 2048, 2048, 1, seed=2)
+    ms, nbytes = handle.bid_sweep_device(t.data_ptr(), 1024, 2048, 2048, use_last_prices=False)
+    assert nbytes == 1024 * 2048 * 4 and ms > 0

@@ -1,0 +1,159 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI (libb200lsap.so), against the
+reference-made golden vectors and the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+import parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _gen(oracle_lib, g):
+    return oracle_lib.generate(int(g["rows"]), int(g["cols"]), int(g["seed"]))
+
+
+@pytest.mark.parametrize("path", parity.golden_cases(max_rows=4096))
+def test_golden_fp32_persistent(handle, oracle_lib, path):
+    g = np.load(path)
+    a = _gen(oracle_lib, g)
+    r2c, prices = handle.solve(np.asfortranarray(a), want_prices=True)  # Eigen's layout
+    eps = 1e-5 / a.shape[1]
+    verdict = parity.check_parity(a, r2c, prices, parity.golden_row_to_col(g), eps)
+    assert verdict == "exact", verdict  # every golden case has a unique optimum: bit-exact expected
+    assert parity.objective(a, r2c) == float(g["objective"])
+
+
+@pytest.mark.parametrize("path", parity.golden_cases(max_rows=1024))
+def test_golden_layouts_dtypes_and_drivers_agree(handle, oracle_lib, path):
+    g = np.load(path)
+    a = _gen(oracle_lib, g)
+    base, p0 = handle.solve(a, want_prices=True)                       # row-major fp32
+    assert np.array_equal(base, parity.golden_row_to_col(g))
+    for variant in (np.asfortranarray(a), a.astype(np.float64), np.asfortranarray(a.astype(np.float64))):
+        r2c, p = handle.solve(variant, want_prices=True)
+        assert np.array_equal(r2c, base) and np.array_equal(p, p0)
+    r2c, p = handle.solve(a, want_prices=True, driver=1)               # host-driven rounds, same kernels
+    assert np.array_equal(r2c, base) and np.array_equal(p, p0)
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (200, 200), (256, 256)])
+def test_square_fixed_eps_and_scaled_eps_both_match(handle, oracle_lib, shape):
+    g = np.load(parity.golden_cases(pattern=f"auction_{shape[0]}x{shape[1]}_s*.npz")[0])
+    a = _gen(oracle_lib, g)
+    ref = parity.golden_row_to_col(g)
+    eps = 1e-5 / a.shape[1]
+    for scaling in (False, True):
+        r2c, prices = handle.solve(a, want_prices=True, eps_scaling=scaling)
+        assert parity.check_parity(a, r2c, prices, ref, eps) == "exact"
+        assert handle.last_stats["eps_final"] == eps
+    assert handle.last_stats["phases"] > 1
+
+
+def test_against_oracle_on_fresh_seeds(handle, oracle_lib):
+    for rows, cols, seed in [(7, 7, 21), (33, 65, 22), (127, 129, 23), (300, 301, 24), (500, 1000, 25),
+                             (96, 4100, 26), (3, 9000, 27)]:
+        a = oracle_lib.generate(rows, cols, seed)
+        out = oracle_lib.oracle_solve(a.astype(np.float64))
+        ref = np.full(rows, -1, np.int64)
+        ref[out["x"]] = out["y"]
+        r2c, prices = handle.solve(a, want_prices=True)
+        parity.check_parity(a, r2c, prices, ref, 1e-5 / cols)
+
+
+def test_zero_means_no_edge(handle, oracle_lib):
+    a = oracle_lib.generate(120, 180, 3)
+    i, j = np.indices(a.shape)
+    a[(j < i) | (j > i + 40)] = 0.0
+    out = oracle_lib.oracle_solve(a.astype(np.float64))
+    ref = np.full(120, -1, np.int64)
+    ref[out["x"]] = out["y"]
+    r2c, prices = handle.solve(np.asfortranarray(a), want_prices=True)
+    assert (a[np.arange(120), r2c] > 0).all()
+    parity.check_parity(a, r2c, prices, ref, 1e-5 / 180)
+
+
+def test_single_edge_rows_use_the_1e6_sentinel(handle, oracle_lib):
+    # a row with one edge bids a + 1e6 + eps (Auction.h:237,250); a diagonal matrix is all such rows
+    a = np.diag(np.linspace(0.1, 1.0, 16)).astype(np.float32)
+    r2c, prices = handle.solve(a, want_prices=True, eps_scaling=False)
+    assert np.array_equal(r2c, np.arange(16))
+    out = oracle_lib.oracle_solve(a.astype(np.float64), want_prices=True)
+    assert np.array_equal(prices, out["prices"])
+    # with eps scaling the rows bid again above the sentinel price and must still terminate
+    assert np.array_equal(handle.solve(a), np.arange(16))
+
+
+def test_ties_go_to_the_lowest_column(handle, oracle_lib):
+    a = np.full((4, 8), 0.5, np.float32)
+    out = oracle_lib.oracle_solve(a.astype(np.float64))
+    r2c, prices = handle.solve(a, want_prices=True)
+    ref = np.full(4, -1, np.int64)
+    ref[out["x"]] = out["y"]
+    parity.check_parity(a, r2c, prices, ref, 1e-5 / 8)
+    one = handle.solve(np.full((1, 8), 0.25, np.float32))
+    assert one[0] == 0
+
+
+def test_error_statuses_instead_of_hanging(handle):
+    import auctionalgorithm_b200 as ab
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve(np.ones((5, 4), np.float32))
+    assert e.value.status == ab.ERR_SHAPE
+    a = np.ones((4, 6), np.float32)
+    a[2] = 0
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve(a)
+    assert e.value.status == ab.ERR_INFEASIBLE
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve(np.ones((4, 6), np.float32), eps_scaling=True)
+    assert e.value.status == ab.ERR_ARG
+    # two rows that can only take the same column: the reference spins, we stop at the watchdog
+    b = np.zeros((2, 3), np.float32)
+    b[:, 1] = 0.5
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve(b, max_rounds=2000)
+    assert e.value.status == ab.ERR_MAX_ROUNDS
+    assert np.array_equal(handle.solve(np.eye(3, dtype=np.float32)), [0, 1, 2])  # handle still usable
+
+
+def test_mirror_classes(handle, oracle_lib):
+    import auctionalgorithm_b200 as ab
+    g = np.load(parity.golden_cases(pattern="auction_200x300_s1.npz")[0])
+    a = np.asfortranarray(_gen(oracle_lib, g).astype(np.float64))
+    edges = ab.Auction.solve(a, handle=handle)
+    assert edges.dtype.itemsize == 24 and len(edges) == 200
+    order = np.argsort(g["x"])
+    assert np.array_equal(edges["y"], g["y"][order]) and ab.objective(edges) == float(g["objective"])
+    mt = ab.AuctionMT.solve(a, 2, handle=handle)
+    assert np.array_equal(mt, edges)  # and, unlike the reference's MT, right for rows < cols
+
+
+def test_deterministic(handle, oracle_lib):
+    a = oracle_lib.generate(700, 700, 5)
+    r1, p1 = handle.solve(a, want_prices=True)
+    r2, p2 = handle.solve(a, want_prices=True)
+    assert np.array_equal(r1, r2) and np.array_equal(p1, p2)
+
+
+def test_c4_full_size_against_reference_golden(handle, oracle_lib):
+    """BASELINE config C4: 16384 x 16384 fp32.  The golden vector is what the unmodified reference
+    (Auction<double> on the widened matrix) returned after 21 minutes of one CPU core."""
+    import os
+    import torch
+    path = os.path.join(parity.GOLDEN_DIR, "auction_16384x16384_s1.npz")
+    if not os.path.exists(path):
+        pytest.skip("C4 golden vector not generated")
+    import auctionalgorithm_b200 as ab
+    g = np.load(path)
+    n = 16384
+    t = torch.empty((n, n), dtype=torch.float32, device="cuda")
+    handle.generate_device(t.data_ptr(), 1, n, n, n, ab.ROW_MAJOR, seed=1)
+    r2c = torch.empty(n, dtype=torch.int32, device="cuda")
+    prices = torch.empty(n, dtype=torch.float64, device="cuda")
+    handle.solve_device(t.data_ptr(), n, n, n, ab.ROW_MAJOR, r2c.data_ptr(), prices.data_ptr())
+    a = t.cpu().numpy()
+    assert np.array_equal(a[:2], oracle_lib.generate(n, n, 1)[:2])  # device generator == host generator
+    got = r2c.cpu().numpy().astype(np.int64)
+    verdict = parity.check_parity(a, got, prices.cpu().numpy(), parity.golden_row_to_col(g), 1e-5 / n)
+    assert parity.objective(a, got) == pytest.approx(float(g["objective"]), abs=n * 1e-5 / n)
+    print("C4 parity:", verdict)

@@ -1,0 +1,41 @@
+"""Scratch timing of the device-resident paths (not the judged bench: see bench.py)."""
+import sys, time, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import auctionalgorithm_b200 as ab
+
+h = ab.Handle(0)
+def dense(rows, cols, seed=1, reps=3, **opt):
+    t = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+    h.generate_device(t.data_ptr(), 1, rows, cols, cols, 1, seed)
+    r2c = torch.empty(rows, dtype=torch.int32, device="cuda")
+    best = None
+    for _ in range(reps):
+        st = h.solve_device(t.data_ptr(), rows, cols, cols, 1, r2c.data_ptr(), **opt)
+        if best is None or st["ms_solve"] < best["ms_solve"]: best = st
+    gbs = best["bid_bytes"] / best["ms_solve"] / 1e6
+    print(f"dense {rows}x{cols} {opt}: {best['ms_solve']:.3f} ms rounds {best['rounds']} bids {best['bids']} phases {best['phases']} "
+          f"us/round {1e3*best['ms_solve']/max(best['rounds'],1):.2f} alg GB/s {gbs:.0f}", flush=True)
+    ms, nb = h.bid_sweep_device(t.data_ptr(), rows, cols, cols, True)
+    ms2, nb = h.bid_sweep_device(t.data_ptr(), rows, cols, cols, True)
+    print(f"   full bid sweep: {ms2:.4f} ms -> {nb/ms2/1e6:.0f} GB/s", flush=True)
+    return r2c
+
+def batch(n, rows=32, cols=48, reps=3):
+    t = torch.empty((n, rows, cols), dtype=torch.float32, device="cuda")
+    h.generate_device(t.data_ptr(), n, rows, cols, cols, 1, 1)
+    out = torch.empty((n, rows), dtype=torch.int32, device="cuda")
+    best = 1e9
+    for _ in range(reps):
+        st = h.solve_batch_device(t.data_ptr(), n, rows, cols, out.data_ptr())
+        best = min(best, st["ms_solve"])
+    print(f"batch {n}x{rows}x{cols}: {best:.3f} ms -> {n/best/1e3:.1f} M problems/s, {st['bid_bytes']/best/1e6:.0f} GB/s", flush=True)
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["c1", "c2", "c3", "sq"]
+    if "c1" in which: dense(200, 300)
+    if "c2" in which: dense(2048, 3072)
+    if "c3" in which: batch(1 << 16); batch(1 << 20)
+    if "sq" in which:
+        dense(2048, 2048); dense(4096, 4096)
+    if "c4" in which: dense(16384, 16384, reps=1)

@@ -1,0 +1,140 @@
+/*
+ * AuctionB200.h — header-only C++ mirror of the reference's solver interface over the C-ABI
+ * (b200lsap.h).  Same names, argument meaning and result types as
+ *
+ *   LSAP::Auction<Scalar, MatrixType>::solve(const MatrixType&)            Auction.h:19-44
+ *   LSAP::AuctionMT<Scalar, MatrixType>::solve(const MatrixType&, size_t)  AuctionMT.h:24-50
+ *   LSAP::AuctionCommon<Scalar>::Edge / Edges                             AuctionCommon.h:30-40
+ *
+ * so a caller such as the reference's driver (LSAP.cpp:41-45,56) only changes the class name:
+ *
+ *   Auction<double>::Edges solution = LSAP::AuctionB200<double>::solve(m);
+ *   solution = LSAP::AuctionMTB200<double>::solve(m, 2);
+ *
+ * MatrixType is any dense matrix with rows(), cols(), data(), outerStride() and operator()(i,j)
+ * plus a compile-time IsRowMajor (every Eigen::Matrix<Scalar,-1,-1[,RowMajor]> qualifies; Eigen
+ * itself is not required by this header).  When AuctionCommon.h has been included before this
+ * header the reference's own Edge type is used, otherwise an identical one is defined.
+ *
+ * Differences from the reference, all on inputs where the reference never returns:
+ * rows > cols, a row without a non-zero coefficient, or an expired round watchdog throw
+ * std::runtime_error.  Edges come back ordered by row (e.x ascending).
+ */
+#ifndef AUCTION_B200_H_
+#define AUCTION_B200_H_
+
+#include <cstddef>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "b200lsap.h"
+
+namespace LSAP
+{
+
+#ifdef AUCTIONCOMMON_H_
+template <typename Scalar> struct B200Types
+{
+    typedef typename AuctionCommon<Scalar>::Edge Edge;
+    typedef typename AuctionCommon<Scalar>::Edges Edges;
+};
+#else
+template <typename Scalar> struct B200Types
+{
+    struct Edge
+    {
+        size_t x;
+        size_t y;
+        Scalar v;
+    };
+    typedef std::vector<Edge> Edges;
+};
+#endif
+
+namespace b200detail
+{
+
+/* one handle per host thread: handles serve one thread at a time (b200lsap.h) */
+inline b200lsap_handle* thread_handle()
+{
+    struct Holder
+    {
+        b200lsap_handle* h = nullptr;
+        ~Holder() { b200lsap_destroy(h); }
+    };
+    static thread_local Holder holder;
+    if (!holder.h)
+    {
+        const int rc = b200lsap_create(&holder.h, -1);
+        if (rc != B200LSAP_OK)
+            throw std::runtime_error(std::string("b200lsap_create: ") + b200lsap_status_string(rc));
+    }
+    return holder.h;
+}
+
+inline int solve_raw(b200lsap_handle* h, const float* a, int64_t r, int64_t c, int64_t ld, int layout,
+                     const b200lsap_options* o, int64_t* out, b200lsap_stats* st)
+{
+    return b200lsap_solve_f32(h, a, r, c, ld, layout, o, out, nullptr, st);
+}
+inline int solve_raw(b200lsap_handle* h, const double* a, int64_t r, int64_t c, int64_t ld, int layout,
+                     const b200lsap_options* o, int64_t* out, b200lsap_stats* st)
+{
+    return b200lsap_solve_f64(h, a, r, c, ld, layout, o, out, nullptr, st);
+}
+
+} // namespace b200detail
+
+template <typename Scalar = double, typename MatrixType = void> class AuctionB200
+{
+public:
+    typedef typename B200Types<Scalar>::Edge Edge;
+    typedef typename B200Types<Scalar>::Edges Edges;
+
+    /* Replaces Auction<Scalar,MatrixType>::solve (Auction.h:44).  opts / stats optional. */
+    template <typename M>
+    static const Edges solve(const M& a, const b200lsap_options* opts = nullptr, b200lsap_stats* stats = nullptr)
+    {
+        const int64_t rows = (int64_t)a.rows(), cols = (int64_t)a.cols();
+        Edges E;
+        if (rows == 0 || cols == 0)
+            return E;
+        std::vector<int64_t> row_to_col((size_t)rows, -1);
+        const int layout = M::IsRowMajor ? B200LSAP_ROW_MAJOR : B200LSAP_COL_MAJOR;
+        b200lsap_handle* h = b200detail::thread_handle();
+        const Scalar* data = a.data();
+        const int rc = b200detail::solve_raw(h, data, rows, cols, (int64_t)a.outerStride(), layout, opts,
+                                             row_to_col.data(), stats);
+        if (rc != B200LSAP_OK)
+            throw std::runtime_error(std::string("AuctionB200::solve: ") + b200lsap_last_error(h));
+        E.resize((size_t)rows);
+        for (int64_t i = 0; i < rows; ++i)
+        {
+            E[(size_t)i].x = (size_t)i;
+            E[(size_t)i].y = (size_t)row_to_col[(size_t)i];
+            E[(size_t)i].v = a(i, row_to_col[(size_t)i]); /* from the caller's matrix: Auction.h:273,283 */
+        }
+        return E;
+    }
+};
+
+/* AuctionMT<Scalar,MatrixType>::solve(m, noOfThreads) (AuctionMT.h:50): noOfThreads is accepted
+ * and ignored — the column-interval split it sized (AuctionMT.h:76-77) is the GPU grid's. */
+template <typename Scalar = double, typename MatrixType = void> class AuctionMTB200
+{
+public:
+    typedef typename B200Types<Scalar>::Edge Edge;
+    typedef typename B200Types<Scalar>::Edges Edges;
+
+    template <typename M> static Edges solve(const M& m, const size_t noOfThreads = 2)
+    {
+        (void)noOfThreads;
+        return AuctionB200<Scalar>::solve(m);
+    }
+};
+
+} // namespace LSAP
+
+#endif /* AUCTION_B200_H_ */

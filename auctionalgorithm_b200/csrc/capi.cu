@@ -55,7 +55,7 @@ struct b200lsap_handle
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;
-    DevBuf a, staging, prices, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
+    DevBuf a, staging, prices, pricesf, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
         ctrl, out64, batch_in, batch_out;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -177,7 +177,7 @@ int b200lsap_destroy(b200lsap_handle* h)
         return B200LSAP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
+    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->pricesf, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
                       &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
                       &h->batch_out})
         b->release();
@@ -272,6 +272,7 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
 template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t cols, int64_t ldp, int total_warps)
 {
     CU(h->prices.ensure((ldp + 512) * sizeof(double)));
+    CU(h->pricesf.ensure((ldp + 512) * sizeof(float)));
     CU(h->profits.ensure(rows * sizeof(double)));
     CU(h->slots.ensure(cols * sizeof(BidSlot)));
     CU(h->owner.ensure(cols * sizeof(int)));
@@ -295,6 +296,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.cols = (int)cols;
     s.cols4 = (int)round_up(cols, 4);
     s.prices = h->prices.as<double>();
+    s.pricesf = h->pricesf.as<float>();
     s.profits = h->profits.as<double>();
     s.slots = h->slots.as<BidSlot>();
     s.owner = h->owner.as<int>();
@@ -347,7 +349,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
 
     CU(cudaEventRecord(h->ev[1], h->stream));
     k_init<T><<<grid, kThreads, 0, h->stream>>>(s, 0);
-    h->launches++;
+    k_absmax<T><<<grid_for(h, plan.rows * (int64_t)(s.cols4 / 4), 256 * 8), 256, 0, h->stream>>>(s.A, s.ld, s.rows, s.cols4,
+                                                                                         s.ctrl);
+    h->launches += 2;
     if (plan.driver == 0)
     {
         void* args[] = {&s};
@@ -792,6 +796,8 @@ int b200lsap_bid_sweep_device_f32(b200lsap_handle* h, const float* a_dev, int64_
     DenseState<float> s = bind_state<float>(h, a_dev, rows, cols, ld);
     s.dry = 1;
     k_init<float><<<grid, kThreads, 0, h->stream>>>(s, keep ? 1 : 0);
+    k_absmax<float><<<grid_for(h, rows * (int64_t)(s.cols4 / 4), 256 * 8), 256, 0, h->stream>>>(s.A, s.ld, s.rows, s.cols4,
+                                                                                        s.ctrl);
     CU(cudaEventRecord(h->ev[1], h->stream));
     k_bid<float><<<grid, kThreads, 0, h->stream>>>(s, 0, (int)rows, 1e-5 / (double)cols);
     CU(cudaEventRecord(h->ev[2], h->stream));

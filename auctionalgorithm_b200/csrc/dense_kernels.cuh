@@ -27,10 +27,11 @@ constexpr int kWarpsPerBlock = kThreads / 32;
 // ---------------------------------------------------------------------------------------------
 // Warp scan of columns [c0, c1) of one row (c0, c1 multiples of 4, row 16-byte aligned):
 // each lane streams 128-bit pieces 512 bytes apart, four in flight, then a shuffle reduction.
+// This is the exact form: every element goes through the double-precision top-2 update.
 // ---------------------------------------------------------------------------------------------
 template <typename T, bool kDeep = false>
-__device__ __forceinline__ Top2<T> scan_segment(const T* __restrict__ row, const double* prices, int c0, int c1,
-                                                int lane)
+__device__ __forceinline__ Top2<T> scan_segment_exact(const T* __restrict__ row, const double* prices, int c0, int c1,
+                                                      int lane)
 {
     using V4 = typename Vec4<T>::type;
     Top2<T> t = top2_empty<T, kDeep>();
@@ -69,6 +70,94 @@ __device__ __forceinline__ Top2<T> scan_segment(const T* __restrict__ row, const
     return t;
 }
 
+// ---------------------------------------------------------------------------------------------
+// fp32 rows: the same scan behind a single-precision filter.  f = a - (float)p is within
+// 2^-23 (amax + pmax) of the exact double a - p, and an element can only change the row's top-2 if
+// its exact value exceeds the row's current second best.  `thr` is a warp-uniform lower bound of
+// that second best, lowered by `margin` >= 2^-21 (amax + pmax + 1): elements with f <= thr are
+// provably irrelevant and cost one FADD and one FMNMX; the few that pass (about 2 ln(cols) per
+// row) take the exact double path of top2_push.  The result is bit-identical to
+// scan_segment_exact; only the instruction count and the L1 price traffic (4 B instead of 8 B
+// per element) change.  Lane l visits its columns in increasing order, as the exact scan does.
+// ---------------------------------------------------------------------------------------------
+template <bool kDeep = false>
+__device__ __forceinline__ Top2<float> scan_segment_filtered(const float* __restrict__ row, const double* prices,
+                                                             const float* pricesf, float margin, int c0, int c1,
+                                                             int lane)
+{
+    Top2<float> t = top2_empty<float, kDeep>();
+    float thr = -CUDART_INF_F;
+    constexpr int U = 4;
+    for (int base = c0; base < c1; base += 128 * U) // warp-uniform trip count
+    {
+        float4 a[U];
+        float m = -CUDART_INF_F;
+#pragma unroll
+        for (int u = 0; u < U; u++)
+        {
+            const int cc = base + u * 128 + lane * 4;
+            a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (cc < c1)
+                a[u] = ld_stream4(row + cc);
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++)
+        {
+            const int cc = base + u * 128 + lane * 4;
+            if (cc < c1)
+            {
+                const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
+                m = fmaxf(m, fmaxf(fmaxf(a[u].x - q.x, a[u].y - q.y), fmaxf(a[u].z - q.z, a[u].w - q.w)));
+            }
+        }
+        if (__any_sync(kFullMask, m > thr))
+        {
+            // rare: redo the subtraction (prices hit L1) and send what passes through the exact update
+#pragma unroll
+            for (int u = 0; u < U; u++)
+            {
+                const int cc = base + u * 128 + lane * 4;
+                if (cc < c1)
+                {
+                    const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
+                    if (a[u].x - q.x > thr)
+                        top2_push(t, a[u].x, prices[cc], cc);
+                    if (a[u].y - q.y > thr)
+                        top2_push(t, a[u].y, prices[cc + 1], cc + 1);
+                    if (a[u].z - q.z > thr)
+                        top2_push(t, a[u].z, prices[cc + 2], cc + 2);
+                    if (a[u].w - q.w > thr)
+                        top2_push(t, a[u].w, prices[cc + 3], cc + 3);
+                }
+            }
+            // second largest of all lanes' (best, second best), rounded down: a lower bound of the
+            // row's second best so far
+            float hi = __double2float_rd(t.v), lo = __double2float_rd(t.w);
+#pragma unroll
+            for (int s = 16; s >= 1; s >>= 1)
+            {
+                const float ohi = __shfl_xor_sync(kFullMask, hi, s);
+                const float olo = __shfl_xor_sync(kFullMask, lo, s);
+                lo = fmaxf(fminf(hi, ohi), fmaxf(lo, olo));
+                hi = fmaxf(hi, ohi);
+            }
+            thr = fmaxf(thr, __fsub_rd(lo, margin));
+        }
+    }
+    top2_warp_reduce(t);
+    return t;
+}
+
+template <typename T, bool kDeep = false>
+__device__ __forceinline__ Top2<T> scan_segment(const DenseState<T>& s, const T* __restrict__ row, float margin, int c0,
+                                                int c1, int lane)
+{
+    if constexpr (sizeof(T) == 4)
+        return scan_segment_filtered<kDeep>(row, s.prices, s.pricesf, margin, c0, c1, lane);
+    else
+        return scan_segment_exact<T, kDeep>(row, s.prices, c0, c1, lane);
+}
+
 // All lanes of the deciding warp.  A row whose every a - p lies at or below -1e6 (possible once
 // a single-edge row has paid the 1e6 sentinel and eps scaling makes it bid again) is re-scanned
 // without the sentinel; with no second candidate it raises its column by exactly eps.
@@ -77,14 +166,15 @@ __device__ __forceinline__ Top2<T> rescue_scan(const DenseState<T>& s, int i, co
 {
     if (t.j >= 0)
         return t;
-    Top2<T> d = scan_segment<T, true>(s.A + (long long)i * s.ld, s.prices, 0, s.cols4, lane);
+    Top2<T> d = scan_segment_exact<T, true>(s.A + (long long)i * s.ld, s.prices, 0, s.cols4, lane);
     if (d.j >= 0 && d.w == -CUDART_INF)
         d.w = fmin(-kNoSecondBest, d.v);
     return d;
 }
 
 // Lane 0 of the deciding warp: record and offer the bid of row i.
-template <typename T> __device__ __forceinline__ void submit_bid(const DenseState<T>& s, int i, const Top2<T>& t, double eps)
+template <typename T>
+__device__ __forceinline__ void submit_bid(const DenseState<T>& s, int i, const Top2<T>& t, double eps, double pmax_seen)
 {
     if (t.j < 0)
     {
@@ -97,7 +187,11 @@ template <typename T> __device__ __forceinline__ void submit_bid(const DenseStat
     s.bid_val[i] = bid;
     s.profits[i] = t.w - eps;                   // Auction.h:253
     if (!s.dry)
+    {
         slot_offer(&s.slots[t.j], bid, i);
+        if (bid > pmax_seen) // rare: prices seldom exceed the largest coefficient
+            atomicMax(reinterpret_cast<unsigned long long*>(&s.ctrl->pmax), (unsigned long long)__double_as_longlong(bid));
+    }
 }
 
 // How many warps share one row this round: 1 while there are at least as many bidders as warps,
@@ -114,8 +208,9 @@ __device__ __forceinline__ int split_factor(int n, int total_warps, int cols4, i
 
 template <typename T>
 __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __restrict__ list, int n, double eps,
-                                          int warp_global, int total_warps, int lane)
+                                          double amax, double pmax, int warp_global, int total_warps, int lane)
 {
+    const float margin = filter_margin(amax, pmax);
     const int S = split_factor(n, total_warps, s.cols4, s.min_seg);
     int seg = (s.cols4 + S - 1) / S;
     seg = (seg + 127) & ~127; // segments start on 512-byte boundaries
@@ -126,12 +221,12 @@ __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __r
         const int i = list[b];
         const int c0 = sg * seg;
         const int c1 = min(c0 + seg, s.cols4);
-        Top2<T> t = scan_segment<T>(s.A + (long long)i * s.ld, s.prices, c0, c1, lane);
+        Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, c0, c1, lane);
         if (S == 1)
         {
             t = rescue_scan(s, i, t, lane);
             if (lane == 0)
-                submit_bid(s, i, t, eps);
+                submit_bid(s, i, t, eps, pmax);
             continue;
         }
         // split row: publish the partial, the last warp to arrive merges all S of them
@@ -157,7 +252,7 @@ __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __r
             if (lane == 0)
             {
                 s.arrive[b] = 0;
-                submit_bid(s, i, m, eps);
+                submit_bid(s, i, m, eps, pmax);
             }
         }
     }
@@ -183,7 +278,9 @@ __device__ __forceinline__ void resolve_phase(const DenseState<T>& s, const int*
                 const unsigned long long key = s.slots[j].key;
                 if (key == row_key(i))
                 {
-                    s.prices[j] = s.bid_val[i]; // Auction.h:259
+                    const double bid = s.bid_val[i];
+                    s.prices[j] = bid; // Auction.h:259
+                    s.pricesf[j] = (float)bid;
                     const int prev = s.owner[j];
                     s.owner[j] = i;
                     s.row2col[i] = j;
@@ -244,6 +341,7 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
     const long long max_rounds = ctrl->max_rounds;
     long long rounds = 0, bids = 0;
     double eps = ctrl->eps[0];
+    const double amax = ctrl->amax;
 
     // phase 0 starts from the state the host prepared: list[0] = all rows, count[0] = rows
     for (;;)
@@ -270,7 +368,7 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
         }
         if (tid == 0)
             ctrl->count[cur ^ 1] = 0;
-        bid_phase<T>(s, s.list[cur], n, eps, warp_global, total_warps, lane);
+        bid_phase<T>(s, s.list[cur], n, eps, amax, fmax(ctrl->pmax, amax), warp_global, total_warps, lane);
         grid.sync();
         // status is only ever raised inside a bid phase: read here, between the two syncs, every
         // thread sees the same value (reading it at the loop top would race with faster CTAs)
@@ -296,12 +394,14 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
 // ---------------------------------------------------------------------------------------------
 template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_bid(DenseState<T> s, int cur, int n, double eps)
 {
+    const double amax = s.ctrl->amax; // written by earlier launches on the stream
+    const double pmax = fmax(s.ctrl->pmax, amax);
     const int lane = threadIdx.x & 31;
     const int warp_global = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     const int total_warps = gridDim.x * kWarpsPerBlock;
     if (blockIdx.x == 0 && threadIdx.x == 0)
         s.ctrl->count[cur ^ 1] = 0;
-    bid_phase<T>(s, s.list[cur], n, eps, warp_global, total_warps, lane);
+    bid_phase<T>(s, s.list[cur], n, eps, amax, pmax, warp_global, total_warps, lane);
 }
 
 template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_resolve(DenseState<T> s, int cur, int n)
@@ -331,9 +431,12 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.arrive[i] = 0;
         s.profits[i] = 1.0; // Auction.h:58
     }
-    if (!keep_prices)
-        for (long long j = tid; j < s.ld; j += n_threads)
-            s.prices[j] = 0.0;
+    for (long long j = tid; j < s.ld + 512; j += n_threads)
+    {
+        const double p = keep_prices && j < s.cols ? s.prices[j] : 0.0;
+        s.prices[j] = p;
+        s.pricesf[j] = (float)p;
+    }
     for (long long j = tid; j < s.cols; j += n_threads)
         s.slots[j] = BidSlot{0ull, 0ull};
     if (tid == 0)
@@ -341,6 +444,9 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.ctrl->count[0] = s.rows;
         s.ctrl->count[1] = 0;
         s.ctrl->status = 0;
+        if (!keep_prices)
+            s.ctrl->pmax = 0.0;
+        s.ctrl->amax = 0.0;
         s.ctrl->phase = 0;
         s.ctrl->rounds = 0;
         s.ctrl->bids = 0;

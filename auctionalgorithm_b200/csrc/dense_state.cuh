@@ -26,8 +26,18 @@ struct DenseCtrl
     long long rounds;
     long long bids;
     long long max_rounds;
+    double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
+    double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)
     double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
 };
+
+// Slack of the single-precision filter of scan_segment_filtered: with |a| <= amax, 0 <= p <= pbound,
+// |fl32(a - fl32(p)) - fl64(a - p)| < 2^-23 (amax + pbound); 2^-21 (amax + pbound + 1) also covers
+// the roundings of the threshold itself.  Rounded up.
+__device__ __forceinline__ float filter_margin(double amax, double pbound)
+{
+    return __double2float_ru((amax + pbound + 1.0) * (1.0 / 2097152.0));
+}
 
 template <typename T> struct DenseState
 {
@@ -37,6 +47,7 @@ template <typename T> struct DenseState
     int cols;
     int cols4; // cols rounded up to 4 (<= ld): scan bound, padding is zero
     double* prices;
+    float* pricesf;  // (float)prices, read by the single-precision filter of the fp32 scan
     double* profits;
     BidSlot* slots;  // [cols]
     int* owner;      // [cols] row holding the column, -1 free
@@ -97,6 +108,31 @@ __global__ void __launch_bounds__(256) k_copy_pad(const T* __restrict__ in, long
         const int c = (int)(e - r * ld_out);
         out[e] = c < cols ? in[r * ld_in + c] : T(0);
     }
+}
+
+// max |a(i,j)| over the padded matrix -> ctrl->amax (non-negative doubles order like their bits).
+// NaNs are ignored, as they are by every comparison of the reference's scan.
+template <typename T>
+__global__ void __launch_bounds__(256) k_absmax(const T* __restrict__ A, long long ld, int rows, int cols4,
+                                                DenseCtrl* ctrl)
+{
+    using V4 = typename Vec4<T>::type;
+    const long long vec_per_row = cols4 / 4;
+    const long long total = (long long)rows * vec_per_row;
+    T m = T(0);
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x)
+    {
+        const long long r = e / vec_per_row, c = (e - r * vec_per_row) * 4;
+        const V4 v = ld_stream4(A + r * ld + c);
+        m = fmax(fmax(m, fabs(v.x)), fmax(fabs(v.y), fmax(fabs(v.z), fabs(v.w))));
+    }
+    double d = (double)m;
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1)
+        d = fmax(d, __shfl_xor_sync(kFullMask, d, s));
+    if ((threadIdx.x & 31) == 0 && d > 0.0)
+        atomicMax(reinterpret_cast<unsigned long long*>(&ctrl->amax), (unsigned long long)__double_as_longlong(d));
 }
 
 // Synthetic inputs, bit-identical to oracle_generate_f32 (include/b200lsap_gen.h).

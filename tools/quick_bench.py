@@ -36,6 +36,12 @@ if __name__ == "__main__":
     if "c1" in which: dense(200, 300)
     if "c2" in which: dense(2048, 3072)
     if "c3" in which: batch(1 << 16); batch(1 << 20)
+    if "sweep" in which:
+        t = torch.empty((16384, 16384), dtype=torch.float32, device="cuda")
+        h.generate_device(t.data_ptr(), 1, 16384, 16384, 16384, 1, 1)
+        for _ in range(4):
+            ms, nb = h.bid_sweep_device(t.data_ptr(), 16384, 16384, 16384, False)
+            print(f"sweep 16384^2: {ms:.4f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
     if "c4" in which: dense(16384, 16384, reps=1)

@@ -15,13 +15,14 @@ OK, ERR_SHAPE, ERR_INFEASIBLE, ERR_MAX_ROUNDS, ERR_CUDA, ERR_ARG, ERR_NO_DEVICE 
 class Options(C.Structure):
     _fields_ = [("eps_multiplier", C.c_double), ("eps_scaling", C.c_int32), ("eps_start", C.c_double),
                 ("eps_factor", C.c_double), ("max_rounds", C.c_int64), ("driver", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("tail_rows", C.c_int32), ("narrow_rows", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [("rounds", C.c_int64), ("bids", C.c_int64), ("phases", C.c_int64), ("bid_bytes", C.c_int64),
                 ("eps_final", C.c_double), ("ms_upload", C.c_double), ("ms_solve", C.c_double),
-                ("ms_download", C.c_double), ("launches", C.c_int64), ("reserved", C.c_int64 * 4)]
+                ("ms_download", C.c_double), ("launches", C.c_int64), ("tail_bids", C.c_int64), ("tail_runs", C.c_int64),
+                ("narrow_rounds", C.c_int64), ("reserved", C.c_int64 * 1)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
@@ -52,6 +53,7 @@ SIGNATURES = {
     "b200lsap_generate_shard_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.c_uint64, C.c_uint64]),
     "b200lsap_bid_sweep_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, C.c_int, C.POINTER(C.c_double),
                                                 C.POINTER(_i64)]),
+    "b200lsap_debug_counters": (C.c_int, [_H, C.POINTER(_i64), C.c_int]),
     "b200lsap_host_alloc": (C.c_void_p, [_i64]),
     "b200lsap_host_free": (None, [_P]),
 }

@@ -40,6 +40,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
     cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    if os.environ.get("B200LSAP_TIMING"):
+        cmd.insert(1, "-DB200LSAP_TIMING")
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
         print(" ".join(cmd))

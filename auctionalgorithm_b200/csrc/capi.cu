@@ -55,7 +55,7 @@ struct b200lsap_handle
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;
-    DevBuf a, staging, prices, pricesf, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
+    DevBuf a, staging, prices, pricesf, cand, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
         ctrl, out64, batch_in, batch_out;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -177,7 +177,7 @@ int b200lsap_destroy(b200lsap_handle* h)
         return B200LSAP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->pricesf, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
+    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->pricesf, &h->cand, &h->narrow, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
                       &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
                       &h->batch_out})
         b->release();
@@ -202,6 +202,16 @@ int b200lsap_set_stream(b200lsap_handle* h, void* s)
         cudaStreamDestroy(h->stream);
     h->stream = static_cast<cudaStream_t>(s);
     h->own_stream = false;
+    return B200LSAP_OK;
+}
+
+/* Cycle counters of the last persistent solve (all zero unless built with -DB200LSAP_TIMING). */
+int b200lsap_debug_counters(const b200lsap_handle* h, int64_t* out, int n)
+{
+    if (!h || !out)
+        return B200LSAP_ERR_ARG;
+    for (int k = 0; k < n && k < 16; k++)
+        out[k] = h->h_ctrl->dbg[k];
     return B200LSAP_OK;
 }
 
@@ -233,6 +243,8 @@ struct DensePlan
     std::vector<double> eps;
     int64_t max_rounds;
     int driver;
+    int tail_rows;
+    int narrow_rows;
 };
 
 // eps schedule (the controller constants of Auction.h:54-55, plus optional scaling).
@@ -266,6 +278,10 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
     plan.cols = cols;
     plan.max_rounds = o.max_rounds > 0 ? o.max_rounds : 20000000;
     plan.driver = o.driver;
+    if (o.tail_rows > kNarrowMax || o.narrow_rows > kNarrowMax)
+        return fail(h, B200LSAP_ERR_ARG, "tail_rows and narrow_rows must be at most 256");
+    plan.tail_rows = o.tail_rows == 0 ? 2 : (o.tail_rows < 0 ? 0 : o.tail_rows);
+    plan.narrow_rows = o.narrow_rows == 0 ? kNarrowMax : (o.narrow_rows < 0 ? 0 : o.narrow_rows);
     return B200LSAP_OK;
 }
 
@@ -273,6 +289,8 @@ template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t 
 {
     CU(h->prices.ensure((ldp + 512) * sizeof(double)));
     CU(h->pricesf.ensure((ldp + 512) * sizeof(float)));
+    CU(h->cand.ensure((size_t)rows * kCand * sizeof(int2)));
+    CU(h->narrow.ensure(sizeof(NarrowCtrl)));
     CU(h->profits.ensure(rows * sizeof(double)));
     CU(h->slots.ensure(cols * sizeof(BidSlot)));
     CU(h->owner.ensure(cols * sizeof(int)));
@@ -297,6 +315,9 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.cols4 = (int)round_up(cols, 4);
     s.prices = h->prices.as<double>();
     s.pricesf = h->pricesf.as<float>();
+    s.cand = h->cand.as<int2>();
+    s.narrow = h->narrow.as<NarrowCtrl>();
+    s.narrow_rows = 0;
     s.profits = h->profits.as<double>();
     s.slots = h->slots.as<BidSlot>();
     s.owner = h->owner.as<int>();
@@ -309,6 +330,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.arrive = h->arrive.as<int>();
     s.ctrl = h->ctrl.as<DenseCtrl>();
     s.min_seg = h->min_seg;
+    s.tail_rows = 0;
     s.dry = 0;
     return s;
 }
@@ -337,6 +359,8 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     if (rc)
         return rc;
     DenseState<T> s = bind_state<T>(h, A, plan.rows, plan.cols, ld);
+    s.tail_rows = plan.tail_rows;
+    s.narrow_rows = plan.narrow_rows;
 
     DenseCtrl* hc = h->h_ctrl;
     memset(hc, 0, sizeof *hc);
@@ -399,6 +423,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         CU(cudaStreamSynchronize(h->stream));
         hc->rounds = rounds;
         hc->bids = bids;
+        hc->gs_bids = hc->gs_episodes = hc->narrow_rounds = 0;
         hc->phase = phase;
     }
     CU(cudaGetLastError());
@@ -411,6 +436,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         stats->rounds = hc->rounds;
         stats->bids = hc->bids;
         stats->phases = hc->phase + 1;
+        stats->narrow_rounds = hc->narrow_rounds;
+        stats->tail_bids = hc->gs_bids;
+        stats->tail_runs = hc->gs_episodes;
         stats->bid_bytes = hc->bids * plan.cols * (int64_t)sizeof(T);
         stats->eps_final = plan.eps.back();
     }

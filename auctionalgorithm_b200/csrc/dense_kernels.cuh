@@ -1,4 +1,4 @@
-// dense_kernels.cuh — the auction round for one dense problem on one GPU.
+// dense_kernels.cuh — the auction for one dense problem on one GPU.
 //
 // A round is the synchronous (Jacobi) form of the reference's Gauss-Seidel sweep:
 //   bid phase      every unassigned row scans its row of A against the same prices
@@ -9,8 +9,17 @@
 //                  owner[col] / row2col[row] arrays in place of the O(|E|) edge scan) and the
 //                  next round's list of unassigned rows is compacted.
 // The controller (Auction.h:44-109: run forward sweeps until nobody is left, eps fixed or
-// scaled) runs on the device in k_auction_persistent; cooperative grid syncs stand where
-// AuctionMT crosses its ThreadBarrier twice per bid (AuctionMT.h:366-368).
+// scaled) runs on the device in k_auction_persistent.  Three regimes, chosen by the number of
+// bidders n of the round (80 % of the rounds of a square problem have fewer than 8 bidders):
+//   n > SMs-1      "wide" round: a warp per row (or per row segment), two cooperative grid syncs
+//                  (AuctionMT crosses its ThreadBarrier twice per bid, AuctionMT.h:366-368);
+//   n <= SMs-1     "narrow" round: one CTA (or 2, 4) scans one bidder's row, CTA 0 is the
+//                  controller: it gathers the n bids, resolves them in shared memory and
+//                  publishes the next round; one flag hand-shake per round, no grid sync;
+//   n <= tail_rows Gauss-Seidel tail: CTA 0 alone, one bid at a time in the reference's own
+//                  schedule, no hand-shake at all.
+// n never grows from one round to the next (a bidder wins and evicts at most one row, or loses
+// and stays), so a phase moves through the regimes in that order.
 #pragma once
 
 #include <cooperative_groups.h>
@@ -21,13 +30,30 @@ namespace b200lsap
 {
 namespace cg = cooperative_groups;
 
+#ifdef B200LSAP_TIMING
+#define TICK(k)                                                                                                    \
+    do                                                                                                             \
+    {                                                                                                              \
+        if (threadIdx.x == 0)                                                                                      \
+        {                                                                                                          \
+            const long long now_ = clock64();                                                                      \
+            sh.dbg[k] += now_ - tick_;                                                                             \
+            tick_ = now_;                                                                                          \
+        }                                                                                                          \
+    } while (0)
+#define TICK_INIT long long tick_ = clock64()
+#else
+#define TICK(k)
+#define TICK_INIT
+#endif
+
 constexpr int kThreads = 1024;        // one CTA per SM, 32 warps
 constexpr int kWarpsPerBlock = kThreads / 32;
 
 // ---------------------------------------------------------------------------------------------
 // Warp scan of columns [c0, c1) of one row (c0, c1 multiples of 4, row 16-byte aligned):
-// each lane streams 128-bit pieces 512 bytes apart, four in flight, then a shuffle reduction.
-// This is the exact form: every element goes through the double-precision top-2 update.
+// each lane streams 128-bit pieces 512 bytes apart, four in flight.  This is the exact form:
+// every element goes through the double-precision top-2 update.  Per-lane result (no reduction).
 // ---------------------------------------------------------------------------------------------
 template <typename T, bool kDeep = false>
 __device__ __forceinline__ Top2<T> scan_segment_exact(const T* __restrict__ row, const double* prices, int c0, int c1,
@@ -66,7 +92,6 @@ __device__ __forceinline__ Top2<T> scan_segment_exact(const T* __restrict__ row,
             top2_push(t, a[u].w, p[u][1].y, cc + 3);
         }
     }
-    top2_warp_reduce(t);
     return t;
 }
 
@@ -75,87 +100,192 @@ __device__ __forceinline__ Top2<T> scan_segment_exact(const T* __restrict__ row,
 // 2^-23 (amax + pmax) of the exact double a - p, and an element can only change the row's top-2 if
 // its exact value exceeds the row's current second best.  `thr` is a warp-uniform lower bound of
 // that second best, lowered by `margin` >= 2^-21 (amax + pmax + 1): elements with f <= thr are
-// provably irrelevant and cost one FADD and one FMNMX; the few that pass (about 2 ln(cols) per
-// row) take the exact double path of top2_push.  The result is bit-identical to
-// scan_segment_exact; only the instruction count and the L1 price traffic (4 B instead of 8 B
-// per element) change.  Lane l visits its columns in increasing order, as the exact scan does.
+// provably irrelevant and cost one FADD and one FMNMX; the few that pass take the exact double
+// path of top2_push.  The result is bit-identical to scan_segment_exact; only the instruction
+// count and the L1 price traffic (4 B instead of 8 B per element) change.  A lane visits its
+// columns in increasing order, as the exact scan does.
+//
+// The initial threshold comes from the row's candidate list (cand_threshold): any two edges of
+// the row bound its second best from below, and the columns that were best at the row's last
+// scans are nearly always still the best.
+//
+// One batch = U 128-bit pieces per lane, piece u at column first + u * stride (a warp scanning a
+// row segment: stride 128, first = base + 4 lane; a whole CTA scanning: stride 4 * threads).
 // ---------------------------------------------------------------------------------------------
-template <bool kDeep = false>
-__device__ __forceinline__ Top2<float> scan_segment_filtered(const float* __restrict__ row, const double* prices,
-                                                             const float* pricesf, float margin, int c0, int c1,
-                                                             int lane)
+template <bool kDeep> struct FilterScan
 {
-    Top2<float> t = top2_empty<float, kDeep>();
-    float thr = -CUDART_INF_F;
-    constexpr int U = 4;
-    for (int base = c0; base < c1; base += 128 * U) // warp-uniform trip count
+    Top2<float> t;
+    float thr;
+    __device__ __forceinline__ explicit FilterScan(float thr0) : t(top2_empty<float, kDeep>()), thr(thr0) {}
+};
+
+constexpr int kScanU = 4;
+
+// warp-wide top-2 of per-lane (hi >= lo) pairs of floats; every lane ends with the result
+__device__ __forceinline__ void warp_top2f(float& hi, float& lo)
+{
+#pragma unroll
+    for (int sft = 16; sft >= 1; sft >>= 1)
     {
-        float4 a[U];
-        float m = -CUDART_INF_F;
-#pragma unroll
-        for (int u = 0; u < U; u++)
-        {
-            const int cc = base + u * 128 + lane * 4;
-            a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (cc < c1)
-                a[u] = ld_stream4(row + cc);
-        }
-#pragma unroll
-        for (int u = 0; u < U; u++)
-        {
-            const int cc = base + u * 128 + lane * 4;
-            if (cc < c1)
-            {
-                const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
-                m = fmaxf(m, fmaxf(fmaxf(a[u].x - q.x, a[u].y - q.y), fmaxf(a[u].z - q.z, a[u].w - q.w)));
-            }
-        }
-        if (__any_sync(kFullMask, m > thr))
-        {
-            // rare: redo the subtraction (prices hit L1) and send what passes through the exact update
-#pragma unroll
-            for (int u = 0; u < U; u++)
-            {
-                const int cc = base + u * 128 + lane * 4;
-                if (cc < c1)
-                {
-                    const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
-                    if (a[u].x - q.x > thr)
-                        top2_push(t, a[u].x, prices[cc], cc);
-                    if (a[u].y - q.y > thr)
-                        top2_push(t, a[u].y, prices[cc + 1], cc + 1);
-                    if (a[u].z - q.z > thr)
-                        top2_push(t, a[u].z, prices[cc + 2], cc + 2);
-                    if (a[u].w - q.w > thr)
-                        top2_push(t, a[u].w, prices[cc + 3], cc + 3);
-                }
-            }
-            // second largest of all lanes' (best, second best), rounded down: a lower bound of the
-            // row's second best so far
-            float hi = __double2float_rd(t.v), lo = __double2float_rd(t.w);
-#pragma unroll
-            for (int s = 16; s >= 1; s >>= 1)
-            {
-                const float ohi = __shfl_xor_sync(kFullMask, hi, s);
-                const float olo = __shfl_xor_sync(kFullMask, lo, s);
-                lo = fmaxf(fminf(hi, ohi), fmaxf(lo, olo));
-                hi = fmaxf(hi, ohi);
-            }
-            thr = fmaxf(thr, __fsub_rd(lo, margin));
-        }
+        const float ohi = __shfl_xor_sync(kFullMask, hi, sft);
+        const float olo = __shfl_xor_sync(kFullMask, lo, sft);
+        lo = fmaxf(fminf(hi, ohi), fmaxf(lo, olo));
+        hi = fmaxf(hi, ohi);
     }
-    top2_warp_reduce(t);
-    return t;
 }
 
-template <typename T, bool kDeep = false>
-__device__ __forceinline__ Top2<T> scan_segment(const DenseState<T>& s, const T* __restrict__ row, float margin, int c0,
-                                                int c1, int lane)
+template <bool kDeep>
+__device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* __restrict__ row,
+                                           const double* prices, const float* pricesf, float margin, int first,
+                                           int stride, int c1)
+{
+    constexpr int U = kScanU;
+    float4 a[U];
+    float m = -INFINITY;
+#pragma unroll
+    for (int u = 0; u < U; u++)
+    {
+        const int cc = first + u * stride;
+        a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (cc < c1)
+            a[u] = ld_stream4(row + cc);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++)
+    {
+        const int cc = first + u * stride;
+        if (cc < c1)
+        {
+            const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
+            m = fmaxf(m, fmaxf(fmaxf(a[u].x - q.x, a[u].y - q.y), fmaxf(a[u].z - q.z, a[u].w - q.w)));
+        }
+    }
+    if (!__any_sync(kFullMask, m > st.thr))
+        return;
+    // Rare path.  First tighten the threshold with the single-precision top-2 of this batch (edges
+    // only: a == 0 is "no edge"): the second largest f of the warp, minus the margin, bounds the
+    // row's exact second best from below.  Then the survivors take the exact update.
+    float hi = -INFINITY, lo = -INFINITY;
+#pragma unroll
+    for (int u = 0; u < U; u++)
+    {
+        const int cc = first + u * stride;
+        if (cc < c1)
+        {
+            const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
+            const float f0 = a[u].x != 0.f ? a[u].x - q.x : -INFINITY;
+            const float f1 = a[u].y != 0.f ? a[u].y - q.y : -INFINITY;
+            const float f2 = a[u].z != 0.f ? a[u].z - q.z : -INFINITY;
+            const float f3 = a[u].w != 0.f ? a[u].w - q.w : -INFINITY;
+            lo = fmaxf(lo, fminf(hi, f0)), hi = fmaxf(hi, f0);
+            lo = fmaxf(lo, fminf(hi, f1)), hi = fmaxf(hi, f1);
+            lo = fmaxf(lo, fminf(hi, f2)), hi = fmaxf(hi, f2);
+            lo = fmaxf(lo, fminf(hi, f3)), hi = fmaxf(hi, f3);
+        }
+    }
+    warp_top2f(hi, lo);
+    const float thr = fmaxf(st.thr, __fsub_rd(lo, margin));
+    st.thr = thr;
+#pragma unroll
+    for (int u = 0; u < U; u++)
+    {
+        const int cc = first + u * stride;
+        if (cc < c1)
+        {
+            const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
+            if (a[u].x - q.x > thr)
+                top2_push(st.t, a[u].x, prices[cc], cc);
+            if (a[u].y - q.y > thr)
+                top2_push(st.t, a[u].y, prices[cc + 1], cc + 1);
+            if (a[u].z - q.z > thr)
+                top2_push(st.t, a[u].z, prices[cc + 2], cc + 2);
+            if (a[u].w - q.w > thr)
+                top2_push(st.t, a[u].w, prices[cc + 3], cc + 3);
+        }
+    }
+}
+
+// Warp-uniform starting threshold of row i from its candidate list (kCand (column, a) pairs left
+// by earlier scans of the row; column -1: empty).  Candidates are true edges of the row, so the
+// second largest of their current values bounds the row's second best from below whatever their
+// age.  fp64 rows are scanned exactly and need none.
+template <typename T>
+__device__ __forceinline__ float cand_threshold(const DenseState<T>& s, int i, float margin, int lane)
 {
     if constexpr (sizeof(T) == 4)
-        return scan_segment_filtered<kDeep>(row, s.prices, s.pricesf, margin, c0, c1, lane);
+    {
+        const int2 raw = __ldcg(s.cand + (long long)i * kCand + lane);
+        float hi = raw.x >= 0 ? __int_as_float(raw.y) - s.pricesf[raw.x] : -INFINITY;
+        float lo = -INFINITY;
+        warp_top2f(hi, lo);
+        return __fsub_rd(lo, margin);
+    }
+    else
+        return -INFINITY;
+}
+
+// Per-lane scan of columns [c0, c1) of a row by one warp (no reduction).
+template <typename T, bool kDeep = false>
+__device__ __forceinline__ Top2<T> scan_segment(const DenseState<T>& s, const T* __restrict__ row, float margin,
+                                                float thr0, int c0, int c1, int lane)
+{
+    if constexpr (sizeof(T) == 4)
+    {
+        FilterScan<kDeep> st(thr0);
+        for (int base = c0; base < c1; base += 128 * kScanU) // warp-uniform trip count
+            scan_batch(st, row, s.prices, s.pricesf, margin, base + lane * 4, 128, c1);
+        return st.t;
+    }
     else
         return scan_segment_exact<T, kDeep>(row, s.prices, c0, c1, lane);
+}
+
+// Per-thread scan of columns [c0, c1) of a row by a whole CTA: thread t takes the 128-bit pieces
+// at columns c0 + 4 t + 4 kThreads k.
+template <typename T>
+__device__ __forceinline__ Top2<T> cta_scan_row(const DenseState<T>& s, const T* __restrict__ row, float margin,
+                                                float thr0, int c0, int c1)
+{
+    if constexpr (sizeof(T) == 4)
+    {
+        FilterScan<false> st(thr0);
+        for (int base = c0; base < c1; base += 4 * kThreads * kScanU)
+            scan_batch(st, row, s.prices, s.pricesf, margin, base + (int)threadIdx.x * 4, 4 * kThreads, c1);
+        return st.t;
+    }
+    else
+    {
+        Top2<T> t = top2_empty<T>();
+        for (int c = c0 + (int)threadIdx.x * 4; c < c1; c += 4 * kThreads)
+        {
+            const auto a = ld_stream4(row + c);
+            top2_push(t, a.x, s.prices[c], c);
+            top2_push(t, a.y, s.prices[c + 1], c + 1);
+            top2_push(t, a.z, s.prices[c + 2], c + 2);
+            top2_push(t, a.w, s.prices[c + 3], c + 3);
+        }
+        return t;
+    }
+}
+
+// Warp reduction that most warps skip: behind a good threshold only a few lanes of a few warps
+// hold a candidate at all.
+template <typename T> __device__ __forceinline__ void top2_warp_reduce_sparse(Top2<T>& t)
+{
+    const unsigned have = __ballot_sync(kFullMask, t.j >= 0);
+    if (have == 0)
+        return;
+    if ((have & (have - 1)) == 0)
+    {
+        // a single lane holds everything
+        const int src = __ffs(have) - 1;
+        t.v = __shfl_sync(kFullMask, t.v, src);
+        t.w = __shfl_sync(kFullMask, t.w, src);
+        t.j = __shfl_sync(kFullMask, t.j, src);
+        t.a = __shfl_sync(kFullMask, t.a, src);
+        return;
+    }
+    top2_warp_reduce(t);
 }
 
 // All lanes of the deciding warp.  A row whose every a - p lies at or below -1e6 (possible once
@@ -167,12 +297,13 @@ __device__ __forceinline__ Top2<T> rescue_scan(const DenseState<T>& s, int i, co
     if (t.j >= 0)
         return t;
     Top2<T> d = scan_segment_exact<T, true>(s.A + (long long)i * s.ld, s.prices, 0, s.cols4, lane);
+    top2_warp_reduce(d);
     if (d.j >= 0 && d.w == -CUDART_INF)
         d.w = fmin(-kNoSecondBest, d.v);
     return d;
 }
 
-// Lane 0 of the deciding warp: record and offer the bid of row i.
+// Lane 0 of the deciding warp: record and offer the bid of row i (wide rounds).
 template <typename T>
 __device__ __forceinline__ void submit_bid(const DenseState<T>& s, int i, const Top2<T>& t, double eps, double pmax_seen)
 {
@@ -206,6 +337,12 @@ __device__ __forceinline__ int split_factor(int n, int total_warps, int cols4, i
     return s;
 }
 
+template <typename T> __device__ __forceinline__ void cand_store(const DenseState<T>& s, int i, int slot, int j, T a)
+{
+    if constexpr (sizeof(T) == 4)
+        __stcg(s.cand + (long long)i * kCand + slot, make_int2(j, __float_as_int(a)));
+}
+
 template <typename T>
 __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __restrict__ list, int n, double eps,
                                           double amax, double pmax, int warp_global, int total_warps, int lane)
@@ -221,15 +358,20 @@ __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __r
         const int i = list[b];
         const int c0 = sg * seg;
         const int c1 = min(c0 + seg, s.cols4);
-        Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, c0, c1, lane);
+        const float thr0 = cand_threshold(s, i, margin, lane);
+        Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, thr0, c0, c1, lane);
         if (S == 1)
         {
+            if (t.j >= 0)
+                cand_store(s, i, (t.j >> 2) & (kCand - 1), t.j, t.a); // = lane: next scan's candidates
+            top2_warp_reduce_sparse(t);
             t = rescue_scan(s, i, t, lane);
             if (lane == 0)
                 submit_bid(s, i, t, eps, pmax);
             continue;
         }
         // split row: publish the partial, the last warp to arrive merges all S of them
+        top2_warp_reduce_sparse(t);
         int ticket = 0;
         if (lane == 0)
         {
@@ -307,6 +449,402 @@ __device__ __forceinline__ void resolve_phase(const DenseState<T>& s, const int*
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Narrow rounds and the Gauss-Seidel tail (n <= SMs - 1 bidders).
+//
+// CTA 0 is the controller, CTAs 1.. are scanners.  Bidder b's row is scanned by P = 1, 2 or 4
+// whole CTAs (P column parts; scanner w serves bidder w / P, part w % P), which merge their 32
+// warps through shared memory and publish one record.  The controller waits for the n * P
+// records, merges the parts (the thread-0 merge of AuctionMT.h:377-398), resolves the n bids in
+// shared memory (highest bid per column, lowest row among equals: the rule of the wide rounds),
+// applies prices / owners / evictions, and posts the next round into the scanners' mailboxes.
+// Rounds with at most tail_rows bidders are finished by the controller alone, Gauss-Seidel.
+// The list is put in increasing row order at entry, so the outcome does not depend on the
+// order in which the wide rounds' atomics compacted it.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ unsigned ld_volatile(const unsigned* p)
+{
+    return *reinterpret_cast<const volatile unsigned*>(p);
+}
+
+__device__ __forceinline__ void prefetch_row_l2(const void* row, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(row), "r"(bytes) : "memory");
+}
+
+template <typename T> struct NarrowShared
+{
+    Top2<T> part[kWarpsPerBlock];
+    int q[kNarrowMax];      // controller: bidders of the round, then the next list
+    int col[kNarrowMax];    // controller: column each bidder bid for
+    double bid[kNarrowMax]; // controller: its bid
+    int warp_count[kWarpsPerBlock];
+    int head, qn, stop;
+    double pmax;
+    long long dbg[16]; // cycle counters (B200LSAP_TIMING builds)
+};
+
+// Every thread of a CTA: scan columns [c0, c1) of row i, merge the CTA's warps.  The result is
+// valid in all lanes of warp 0.  Also refreshes the row's candidate list.
+template <typename T>
+__device__ __forceinline__ Top2<T> cta_bid_scan(const DenseState<T>& s, NarrowShared<T>& sh, int i, float margin, int c0,
+                                                int c1)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#ifdef B200LSAP_TIMING
+    long long tick_ = clock64();
+    const bool timed_ = blockIdx.x == 0;
+#define TICKB(k)                                                                                                   \
+    do                                                                                                             \
+    {                                                                                                              \
+        if (timed_ && threadIdx.x == 0)                                                                            \
+        {                                                                                                          \
+            const long long now_ = clock64();                                                                      \
+            sh.dbg[k] += now_ - tick_;                                                                             \
+            tick_ = now_;                                                                                          \
+        }                                                                                                          \
+    } while (0)
+#else
+#define TICKB(k)
+#endif
+    const float thr0 = cand_threshold(s, i, margin, lane);
+    TICKB(8);
+    Top2<T> t = cta_scan_row(s, s.A + (long long)i * s.ld, margin, thr0, c0, c1);
+    TICKB(9);
+    top2_warp_reduce_sparse(t);
+    if (lane == 0)
+        sh.part[warp] = t;
+    TICKB(10);
+    __syncthreads();
+    TICKB(11);
+    Top2<T> m = top2_empty<T>();
+    if (warp == 0)
+    {
+        m = sh.part[lane];
+        // candidates: a column always lives in slot (column / 4) % kCand, so the list never holds
+        // an edge twice; of the warp results that share a slot the best one is kept
+        if constexpr (sizeof(T) == 4)
+        {
+            const int slot = m.j >= 0 ? (m.j >> 2) & (kCand - 1) : -1 - lane;
+            bool keep = m.j >= 0;
+            for (int k = 0; k < 32; k++)
+            {
+                const double ov = __shfl_sync(kFullMask, m.v, k);
+                const int oslot = __shfl_sync(kFullMask, slot, k);
+                keep = keep && !(oslot == slot && (ov > m.v || (ov == m.v && k < lane)));
+            }
+            if (keep)
+                cand_store(s, i, slot, m.j, m.a);
+        }
+        top2_warp_reduce_sparse(m);
+    }
+    return m;
+}
+
+// Scanner CTAs.  `last` is the last mailbox flag this CTA has consumed (kept across phases).
+template <typename T>
+__device__ __forceinline__ void narrow_scanner(const DenseState<T>& s, NarrowShared<T>& sh, int& last, double amax)
+{
+    NarrowSlot* slot = &s.narrow->slot[blockIdx.x - 1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (;;)
+    {
+        if (threadIdx.x == 0)
+        {
+            int f;
+            while ((f = ld_volatile(&slot->flag)) == last)
+                __nanosleep(32);
+            __threadfence();
+            sh.head = f;
+        }
+        __syncthreads();
+        last = sh.head;
+        if (last < 0)
+            return; // the controller finished the phase (or stopped on an error)
+        const int i = ld_volatile(&slot->row);
+        const int c0 = ld_volatile(&slot->c0), c1 = ld_volatile(&slot->c1);
+        const float margin = filter_margin(amax, *reinterpret_cast<const volatile double*>(&slot->pmax));
+        Top2<T> m = cta_bid_scan(s, sh, i, margin, c0, c1);
+        if (warp == 0 && lane == 0)
+        {
+            slot->v = m.v;
+            slot->w = m.w;
+            slot->a = (double)m.a;
+            slot->j = m.j;
+            __threadfence();
+            atomicAdd(&s.narrow->arrived, 1u);
+        }
+        __syncthreads(); // sh.part / sh.head are reused next round
+    }
+}
+
+// Gauss-Seidel tail on the controller: the queue sh.q[head .. head+qn) is served FIFO, one bid at a
+// time (Auction.h:220-285), until it is empty.  Returns the bids placed.
+template <typename T>
+__device__ __forceinline__ long long gs_tail(const DenseState<T>& s, NarrowShared<T>& sh, double eps, double amax,
+                                             long long budget)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned row_bytes = (unsigned)(s.cols4 * sizeof(T));
+    const bool can_prefetch = (row_bytes & 15u) == 0 && ((s.ld * sizeof(T)) & 15u) == 0;
+    if (tid > 0 && tid < sh.qn && can_prefetch)
+        prefetch_row_l2(s.A + (long long)sh.q[(sh.head + tid) & (kNarrowMax - 1)] * s.ld, row_bytes);
+    long long done = 0;
+    for (;;)
+    {
+        const int qn = sh.qn, head = sh.head;
+        if (qn == 0 || sh.stop || done >= budget)
+            break;
+        const int i = sh.q[head & (kNarrowMax - 1)];
+        const float margin = filter_margin(amax, sh.pmax);
+        TICK_INIT;
+        Top2<T> m = cta_bid_scan(s, sh, i, margin, 0, s.cols4);
+        TICK(0);
+        if (warp == 0)
+        {
+            m = rescue_scan(s, i, m, lane);
+            if (lane == 0)
+            {
+                if (m.j < 0)
+                {
+                    s.ctrl->status = 2; // B200LSAP_ERR_INFEASIBLE
+                    sh.stop = 1;
+                }
+                else
+                {
+                    const double bid = (double)m.a - m.w + eps; // Auction.h:250
+                    s.profits[i] = m.w - eps;                   // Auction.h:253
+                    s.prices[m.j] = bid;                        // Auction.h:259
+                    s.pricesf[m.j] = (float)bid;
+                    const int prev = s.owner[m.j];
+                    s.owner[m.j] = i;
+                    s.row2col[i] = m.j;
+                    int left = qn - 1;
+                    if (prev >= 0)
+                    {
+                        s.row2col[prev] = -1; // Auction.h:270
+                        sh.q[(head + qn) & (kNarrowMax - 1)] = prev;
+                        left++;
+                        if (can_prefetch && left > 1)
+                            prefetch_row_l2(s.A + (long long)prev * s.ld, row_bytes);
+                    }
+                    sh.head = head + 1;
+                    sh.qn = left;
+                    if (bid > sh.pmax)
+                        sh.pmax = bid;
+                }
+            }
+        }
+        TICK(1);
+        __syncthreads();
+        TICK(2);
+        done++;
+    }
+    return done;
+}
+
+struct NarrowCounts
+{
+    long long rounds, bids, gs_bids, gs_runs;
+};
+
+// Controller CTA: finishes the eps phase that list[0..n) is the tail of.  On return the list is
+// empty unless the watchdog or an error stopped it (then ctrl->status is set).
+template <typename T>
+__device__ __forceinline__ void narrow_controller(const DenseState<T>& s, NarrowShared<T>& sh,
+                                                  const int* __restrict__ list, int n, int& seq, int mode_count,
+                                                  double eps, double amax, long long budget, NarrowCounts& cnt)
+{
+    NarrowCtrl* nc = s.narrow;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int scanners = gridDim.x - 1;
+    // entry: bidders in increasing row order (rank sort, n <= kNarrowMax)
+    if (tid < n)
+    {
+        const int mine = list[tid];
+        int rank = 0;
+        for (int k = 0; k < n; k++)
+            rank += list[k] < mine;
+        sh.q[rank] = mine;
+    }
+    if (tid == 0)
+    {
+        sh.head = 0;
+        sh.qn = n;
+        sh.stop = 0;
+        sh.pmax = fmax(*reinterpret_cast<volatile double*>(&s.ctrl->pmax), amax);
+    }
+    if (tid < 16)
+        sh.dbg[tid] = 0;
+    __syncthreads();
+    unsigned target = ld_volatile(&nc->arrived);
+    const long long spent0 = cnt.rounds + cnt.gs_bids;
+    for (;;)
+    {
+        n = sh.qn;
+        if (n == 0 || sh.stop)
+            break;
+        const long long left_budget = budget - (cnt.rounds + cnt.gs_bids - spent0);
+        if (left_budget <= 0)
+        {
+            if (tid == 0)
+                s.ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS
+            break;
+        }
+        if (n <= s.tail_rows || n > s.narrow_rows || n > scanners)
+        {
+            cnt.gs_bids += gs_tail(s, sh, eps, amax, left_budget);
+            cnt.gs_runs++;
+            if (sh.qn != 0 && !sh.stop && tid == 0)
+                s.ctrl->status = 3; // stopped on the watchdog
+            break;
+        }
+        // ---- publish the round (the queue is compacted to q[0..n) at this point, head == 0) -----
+        int parts = 1;
+        while (parts < 4 && n * parts * 2 <= scanners && (s.cols4 + parts * 2 - 1) / (parts * 2) >= 4 * kThreads)
+            parts *= 2;
+        TICK_INIT;
+        ++seq;
+        if (tid < n * parts)
+        {
+            const int b = tid / parts, part = tid - b * parts;
+            int seg = (s.cols4 + parts - 1) / parts;
+            seg = (seg + 127) & ~127;
+            NarrowSlot* slot = &nc->slot[tid];
+            slot->row = sh.q[b];
+            slot->c0 = part * seg;
+            slot->c1 = min(part * seg + seg, s.cols4);
+            slot->pmax = sh.pmax;
+            __threadfence();
+            *reinterpret_cast<volatile int*>(&slot->flag) = seq;
+        }
+        if (tid == 0)
+        {
+            target += (unsigned)(n * parts);
+            while ((int)(ld_volatile(&nc->arrived) - target) < 0)
+                ;
+            __threadfence();
+        }
+        TICK(4);
+        __syncthreads();
+        // ---- gather: one thread per bidder merges its parts (AuctionMT.h:377-398) ---------------
+        int my_row = -1, my_col = -1, my_prev = -1;
+        double my_bid = 0.0, my_w = 0.0;
+        if (tid < n)
+        {
+            my_row = sh.q[tid];
+            Top2<double> m;
+            m.v = m.w = -kNoSecondBest;
+            m.j = -1;
+            m.a = 0.0;
+            for (int p = 0; p < parts; p++)
+            {
+                const NarrowSlot* r = &nc->slot[tid * parts + p];
+                Top2<double> o;
+                o.v = __ldcg(&r->v);
+                o.w = __ldcg(&r->w);
+                o.a = __ldcg(&r->a);
+                o.j = __ldcg(&r->j);
+                top2_merge(m, o);
+            }
+            if (m.j < 0)
+                sh.stop = 2; // nothing above the -1e6 sentinel: needs the deep re-scan of the tail
+            else
+            {
+                my_col = m.j;
+                my_w = m.w;
+                my_bid = m.a - m.w + eps; // Auction.h:250; m.a is the exactly widened coefficient
+            }
+            sh.col[tid] = my_col;
+            sh.bid[tid] = my_bid;
+        }
+        __syncthreads();
+        TICK(5);
+        if (sh.stop == 2)
+        {
+            // hand the whole queue to the Gauss-Seidel tail, which knows the rescue path
+            __syncthreads();
+            if (tid == 0)
+                sh.stop = 0;
+            __syncthreads();
+            cnt.gs_bids += gs_tail(s, sh, eps, amax, left_budget);
+            cnt.gs_runs++;
+            if (sh.qn != 0 && !sh.stop && tid == 0)
+                s.ctrl->status = 3;
+            break;
+        }
+        // ---- resolve in shared memory: highest bid per column, lowest row among equal bids -------
+        bool win = false;
+        if (tid < n)
+        {
+            win = true;
+            for (int k = 0; k < n; k++)
+                if (k != tid && sh.col[k] == my_col)
+                {
+                    const double ob = sh.bid[k];
+                    const int orow = sh.q[k];
+                    if (ob > my_bid || (ob == my_bid && orow < my_row))
+                        win = false;
+                }
+            s.profits[my_row] = my_w - eps; // Auction.h:253
+            if (win)
+            {
+                s.prices[my_col] = my_bid; // Auction.h:259
+                s.pricesf[my_col] = (float)my_bid;
+                my_prev = s.owner[my_col];
+                s.owner[my_col] = my_row;
+                s.row2col[my_row] = my_col;
+                if (my_prev >= 0)
+                    s.row2col[my_prev] = -1; // Auction.h:270
+            }
+        }
+        // ---- next list, in bidder order: a loser stays, a winner hands its place to the row it evicted
+        const int push = tid < n ? (win ? my_prev : my_row) : -1;
+        const unsigned mask = __ballot_sync(kFullMask, push >= 0);
+        if (lane == 0)
+            sh.warp_count[warp] = __popc(mask);
+        double bmax = (tid < n && win) ? my_bid : 0.0;
+#pragma unroll
+        for (int sft = 16; sft >= 1; sft >>= 1)
+            bmax = fmax(bmax, __shfl_xor_sync(kFullMask, bmax, sft));
+        __syncthreads(); // everybody has read sh.q / sh.col / sh.bid, warp_count is complete
+        int base = 0, total = 0;
+        for (int k = 0; k < kWarpsPerBlock; k++)
+        {
+            const int c = sh.warp_count[k];
+            base += k < warp ? c : 0;
+            total += c;
+        }
+        if (push >= 0)
+            sh.q[base + __popc(mask & ((1u << lane) - 1))] = push;
+        if (lane == 0 && bmax > 0.0)
+            atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax), (unsigned long long)__double_as_longlong(bmax));
+        if (tid == 0)
+        {
+            sh.head = 0;
+            sh.qn = total;
+        }
+        cnt.rounds++;
+        cnt.bids += n;
+        __syncthreads();
+        TICK(6);
+    }
+    // release the scanners: a negative flag, different from the one of the previous narrow mode
+    __syncthreads();
+    if (tid < scanners)
+    {
+        __threadfence();
+        *reinterpret_cast<volatile int*>(&nc->slot[tid].flag) = -mode_count;
+    }
+    if (tid == 0 && sh.pmax > s.ctrl->pmax)
+        s.ctrl->pmax = sh.pmax;
+#ifdef B200LSAP_TIMING
+    if (tid < 16)
+        s.ctrl->dbg[tid] += sh.dbg[tid];
+#endif
+}
+
 // Start of an eps phase: prices are kept, every assignment is dropped, all rows bid again.
 template <typename T>
 __device__ __forceinline__ void reset_phase(const DenseState<T>& s, int* __restrict__ list, long long tid,
@@ -334,14 +872,19 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
     const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
     const long long n_threads = (long long)gridDim.x * kThreads;
     volatile DenseCtrl* ctrl = s.ctrl;
+    __shared__ NarrowShared<T> narrow_sh;
 
     int cur = 0;
     int phase = 0;
+    int seq = 0;        // CTA 0: sequence number of the last narrow round; scanners: last mailbox flag consumed
+    int mode_count = 0; // times the grid has entered narrow mode
     const int n_phases = ctrl->n_phases;
     const long long max_rounds = ctrl->max_rounds;
     long long rounds = 0, bids = 0;
+    NarrowCounts ncnt{0, 0, 0, 0};
     double eps = ctrl->eps[0];
     const double amax = ctrl->amax;
+    const int narrow_rows = min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
 
     // phase 0 starts from the state the host prepared: list[0] = all rows, count[0] = rows
     for (;;)
@@ -360,11 +903,29 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
             grid.sync();
             continue;
         }
-        if (rounds >= max_rounds)
+        const long long spent = rounds + ncnt.rounds + ncnt.gs_bids;
+        if (spent >= max_rounds)
         {
             if (tid == 0)
                 ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS
             break;
+        }
+        if (n <= narrow_rows || n <= min(s.tail_rows, kNarrowMax))
+        {
+            // narrow rounds / Gauss-Seidel tail: finishes the phase without a grid sync per round
+            mode_count++;
+            if (blockIdx.x == 0)
+                narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent,
+                                     ncnt);
+            else
+                narrow_scanner<T>(s, narrow_sh, seq, amax);
+            grid.sync();
+            if (ctrl->status != 0)
+                break;
+            if (tid == 0)
+                ctrl->count[cur] = 0;
+            grid.sync();
+            continue;
         }
         if (tid == 0)
             ctrl->count[cur ^ 1] = 0;
@@ -382,14 +943,17 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
     }
     if (tid == 0)
     {
-        ctrl->rounds = rounds;
-        ctrl->bids = bids;
+        ctrl->rounds = rounds + ncnt.rounds;
+        ctrl->bids = bids + ncnt.bids + ncnt.gs_bids;
+        ctrl->narrow_rounds = ncnt.rounds;
+        ctrl->gs_bids = ncnt.gs_bids;
+        ctrl->gs_episodes = ncnt.gs_runs;
         ctrl->phase = phase;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// Host-driven form of the same round (options.driver = 1, and the standalone bidding sweep
+// Host-driven form of the wide round (options.driver = 1, and the standalone bidding sweep
 // that ncu and bench.py time): identical device code, one launch per phase of a round.
 // ---------------------------------------------------------------------------------------------
 template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_bid(DenseState<T> s, int cur, int n, double eps)
@@ -439,6 +1003,8 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
     }
     for (long long j = tid; j < s.cols; j += n_threads)
         s.slots[j] = BidSlot{0ull, 0ull};
+    for (long long k = tid; k < (long long)s.rows * kCand; k += n_threads)
+        s.cand[k] = make_int2(-1, 0);
     if (tid == 0)
     {
         s.ctrl->count[0] = s.rows;
@@ -450,7 +1016,10 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.ctrl->phase = 0;
         s.ctrl->rounds = 0;
         s.ctrl->bids = 0;
+        s.narrow->arrived = 0u;
     }
+    if (tid < kNarrowMax)
+        s.narrow->slot[tid].flag = 0;
 }
 
 // int32 row2col -> int64 for the host ABI, and price export

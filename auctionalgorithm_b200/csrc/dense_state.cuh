@@ -14,6 +14,8 @@ namespace b200lsap
 {
 
 constexpr int kMaxPhases = 48;
+constexpr int kCand = 32;       // candidate (column, a) pairs kept per row: slot = (column / 4) % 32
+constexpr int kNarrowMax = 256; // power of two >= the largest narrow round (SMs - 1 bidders)
 
 // Controller block, one per solve, in device memory (mirrored to pinned host memory at the end).
 struct DenseCtrl
@@ -26,6 +28,10 @@ struct DenseCtrl
     long long rounds;
     long long bids;
     long long max_rounds;
+    long long narrow_rounds; // rounds run by the controller / scanner hand-shake (included in rounds)
+    long long gs_bids;      // bids placed by the Gauss-Seidel tail (included in bids)
+    long long gs_episodes;  // times the tail ran
+    long long dbg[16];      // cycle counters of the narrow rounds / tail (B200LSAP_TIMING builds)
     double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)
     double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
@@ -38,6 +44,29 @@ __device__ __forceinline__ float filter_margin(double amax, double pbound)
 {
     return __double2float_ru((amax + pbound + 1.0) * (1.0 / 2097152.0));
 }
+
+// Narrow rounds: one mailbox per scanner CTA, each on its own 128-byte line so that a spinning
+// scanner loads a line nobody else touches (148 SMs polling ONE address slowed every L2 access of
+// the controller several-fold).  The controller fills the request and then sets `flag`; the scanner
+// answers in place and bumps NarrowCtrl::arrived.
+struct __align__(128) NarrowSlot
+{
+    int flag;  // > 0: sequence number of the round to serve; < 0: leave narrow mode
+    int row;   // bidder row
+    int c0, c1; // columns to scan
+    double pmax; // price bound for the filter margin
+    // answer
+    double v, w, a; // best value, second best value, coefficient of the best (widened exactly)
+    int j;          // its column, -1: nothing found in this part
+    int pad[15];
+};
+
+struct NarrowCtrl
+{
+    unsigned arrived; // monotone count of answers published by scanners
+    int pad[31];
+    NarrowSlot slot[kNarrowMax];
+};
 
 template <typename T> struct DenseState
 {
@@ -59,6 +88,10 @@ template <typename T> struct DenseState
     int* arrive;     // [rows] split-row arrival counters (zero between rounds)
     DenseCtrl* ctrl;
     int min_seg;     // smallest row segment a warp takes when rows are split (multiple of 128)
+    int2* cand;      // [rows][kCand] (column, bits of a): edges that were among the row's best, -1: empty
+    NarrowCtrl* narrow;
+    int narrow_rows; // a round with at most this many bidders (and at most SMs - 1) runs as a narrow round
+    int tail_rows;   // a round with at most this many bidders is finished by the Gauss-Seidel tail (0: never)
     int dry;         // 1: measurement sweep, bids are computed and stored but not offered
 };
 

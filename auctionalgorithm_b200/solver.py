@@ -62,7 +62,7 @@ class Handle:
 
     @staticmethod
     def _opts(eps_multiplier=None, eps_scaling=None, eps_start=None, eps_factor=None, max_rounds=None,
-              driver=None) -> Options:
+              driver=None, tail_rows=None, narrow_rows=None) -> Options:
         o = Options()
         _capi.lib().b200lsap_options_default(C.byref(o))
         if eps_multiplier is not None:
@@ -77,6 +77,10 @@ class Handle:
             o.max_rounds = max_rounds
         if driver is not None:
             o.driver = driver
+        if tail_rows is not None:
+            o.tail_rows = tail_rows
+        if narrow_rows is not None:
+            o.narrow_rows = narrow_rows
         return o
 
     def set_stream(self, cuda_stream: int):
@@ -152,6 +156,11 @@ class Handle:
                               seed: int, problem: int = 0):
         self._check(self._lib.b200lsap_generate_shard_device_f32(self._h, C.c_void_p(a_ptr), rows, cols_local, ld,
                                                                  col0, cols_global, seed, problem))
+
+    def debug_counters(self):
+        out = (C.c_int64 * 16)()
+        self._check(self._lib.b200lsap_debug_counters(self._h, out, 16))
+        return list(out)
 
     def bid_sweep_device(self, a_ptr: int, rows: int, cols: int, ld: int, use_last_prices: bool = True):
         ms = C.c_double(0)

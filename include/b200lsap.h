@@ -67,6 +67,12 @@ typedef struct
     int64_t max_rounds;    /* watchdog; <= 0: default */
     int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
                               of a round, driven from the host (profiling and cross-checks) */
+    int32_t tail_rows;     /* a round with at most this many bidders is finished by the Gauss-Seidel
+                              tail on one SM, one bid at a time; 0: default (2), -1: never, at most
+                              256.  Persistent driver only. */
+    int32_t narrow_rows;   /* a round with at most this many bidders (and at most SMs - 1) runs as a
+                              narrow round: one CTA per bidder row, a controller CTA instead of grid
+                              syncs; 0: default (SMs - 1), -1: never.  Persistent driver only. */
     int32_t reserved;
 } b200lsap_options;
 
@@ -81,7 +87,10 @@ typedef struct
     double ms_solve;   /* auction kernels only, CUDA events on the handle's stream */
     double ms_download;
     int64_t launches;  /* kernels launched by this call */
-    int64_t reserved[4];
+    int64_t tail_bids; /* bids placed by the Gauss-Seidel tail (included in bids, not in rounds) */
+    int64_t tail_runs; /* times the tail took over */
+    int64_t narrow_rounds; /* rounds run as narrow rounds (included in rounds) */
+    int64_t reserved[1];
 } b200lsap_stats;
 
 /* device < 0: the current CUDA device.  Creates the handle's own non-blocking stream. */
@@ -148,6 +157,10 @@ int b200lsap_generate_shard_device_f32(b200lsap_handle* handle, float* a_dev, in
  * ms_out the CUDA-event time of that single kernel; bytes_out = rows*cols*sizeof(float). */
 int b200lsap_bid_sweep_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols,
                                   int64_t ld, int use_last_prices, double* ms_out, int64_t* bytes_out);
+
+/* Developer aid: cycle counters of the narrow rounds / tail of the last dense solve; all zero
+ * unless the library was built with -DB200LSAP_TIMING.  out: up to 16 values. */
+int b200lsap_debug_counters(const b200lsap_handle* handle, int64_t* out, int n);
 
 /* Pinned host memory for callers that want full-rate PCIe copies. */
 void* b200lsap_host_alloc(int64_t bytes);

@@ -32,8 +32,13 @@ def test_golden_layouts_dtypes_and_drivers_agree(handle, oracle_lib, path):
     for variant in (np.asfortranarray(a), a.astype(np.float64), np.asfortranarray(a.astype(np.float64))):
         r2c, p = handle.solve(variant, want_prices=True)
         assert np.array_equal(r2c, base) and np.array_equal(p, p0)
-    r2c, p = handle.solve(a, want_prices=True, driver=1)               # host-driven rounds, same kernels
-    assert np.array_equal(r2c, base) and np.array_equal(p, p0)
+    # host-driven rounds run the same device code without the Gauss-Seidel tail: identical to the
+    # persistent kernel with the tail switched off, price for price
+    r2c_j, p_j = handle.solve(a, want_prices=True, tail_rows=-1, narrow_rows=-1)
+    assert handle.last_stats["tail_bids"] == 0 and handle.last_stats["narrow_rounds"] == 0
+    r2c, p = handle.solve(a, want_prices=True, driver=1)
+    assert np.array_equal(r2c, r2c_j) and np.array_equal(p, p_j)
+    assert np.array_equal(r2c_j, base)
 
 
 @pytest.mark.parametrize("shape", [(64, 64), (200, 200), (256, 256)])

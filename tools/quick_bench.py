@@ -14,8 +14,11 @@ def dense(rows, cols, seed=1, reps=3, **opt):
         st = h.solve_device(t.data_ptr(), rows, cols, cols, 1, r2c.data_ptr(), **opt)
         if best is None or st["ms_solve"] < best["ms_solve"]: best = st
     gbs = best["bid_bytes"] / best["ms_solve"] / 1e6
-    print(f"dense {rows}x{cols} {opt}: {best['ms_solve']:.3f} ms rounds {best['rounds']} bids {best['bids']} phases {best['phases']} "
+    print(f"dense {rows}x{cols} {opt}: {best['ms_solve']:.3f} ms rounds {best['rounds']} bids {best['bids']} phases {best['phases']} narrow {best['narrow_rounds']} tail {best['tail_bids']}/{best['tail_runs']} "
           f"us/round {1e3*best['ms_solve']/max(best['rounds'],1):.2f} alg GB/s {gbs:.0f}", flush=True)
+    dbg = h.debug_counters()
+    if any(dbg):
+        print("   dbg cycles:", dbg, flush=True)
     ms, nb = h.bid_sweep_device(t.data_ptr(), rows, cols, cols, True)
     ms2, nb = h.bid_sweep_device(t.data_ptr(), rows, cols, cols, True)
     print(f"   full bid sweep: {ms2:.4f} ms -> {nb/ms2/1e6:.0f} GB/s", flush=True)
@@ -44,4 +47,14 @@ if __name__ == "__main__":
             print(f"sweep 16384^2: {ms:.4f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
+    if "c4d" in which:
+        dense(16384, 16384, reps=1)
+        dense(16384, 16384, reps=1, tail_rows=8)
+    if "c4" in which:
+        for opt in (dict(), dict(tail_rows=1), dict(tail_rows=4), dict(tail_rows=8), dict(narrow_rows=-1, tail_rows=8),
+                    dict(narrow_rows=-1, tail_rows=-1)):
+            dense(16384, 16384, reps=2, **opt)
+    if "c4d" in which:
+        dense(16384, 16384, reps=1)
+        dense(16384, 16384, reps=1, tail_rows=8)
     if "c4" in which: dense(16384, 16384, reps=1)

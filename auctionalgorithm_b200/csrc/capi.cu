@@ -61,6 +61,7 @@ struct b200lsap_handle
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t last_cols = 0; // prices of the last dense solve are valid for this many columns
     int min_seg = 512;
+    int max_parts = 4;
     int64_t launches = 0;
 };
 
@@ -161,6 +162,12 @@ int b200lsap_create(b200lsap_handle** out, int device)
     h->own_stream = true;
     for (auto& e : h->ev)
         cudaEventCreate(&e);
+    if (const char* s = getenv("B200LSAP_MAX_PARTS"))
+    {
+        int v = atoi(s);
+        if (v >= 1 && v <= 64)
+            h->max_parts = v;
+    }
     if (const char* s = getenv("B200LSAP_MIN_SEG"))
     {
         int v = atoi(s);
@@ -280,7 +287,7 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
     plan.driver = o.driver;
     if (o.tail_rows > kNarrowMax || o.narrow_rows > kNarrowMax)
         return fail(h, B200LSAP_ERR_ARG, "tail_rows and narrow_rows must be at most 256");
-    plan.tail_rows = o.tail_rows == 0 ? 2 : (o.tail_rows < 0 ? 0 : o.tail_rows);
+    plan.tail_rows = o.tail_rows == 0 ? 1 : (o.tail_rows < 0 ? 0 : o.tail_rows);
     plan.narrow_rows = o.narrow_rows == 0 ? kNarrowMax : (o.narrow_rows < 0 ? 0 : o.narrow_rows);
     return B200LSAP_OK;
 }
@@ -318,6 +325,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.cand = h->cand.as<int2>();
     s.narrow = h->narrow.as<NarrowCtrl>();
     s.narrow_rows = 0;
+    s.max_parts = h->max_parts;
     s.profits = h->profits.as<double>();
     s.slots = h->slots.as<BidSlot>();
     s.owner = h->owner.as<int>();

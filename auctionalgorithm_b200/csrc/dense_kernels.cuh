@@ -358,7 +358,9 @@ __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __r
         const int i = list[b];
         const int c0 = sg * seg;
         const int c1 = min(c0 + seg, s.cols4);
-        const float thr0 = cand_threshold(s, i, margin, lane);
+        // a whole row per warp tightens its own threshold after the first of many batches; the
+        // candidate list (one more dependent L2 access) pays only for short segments
+        const float thr0 = S == 1 ? -INFINITY : cand_threshold(s, i, margin, lane);
         Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, thr0, c0, c1, lane);
         if (S == 1)
         {
@@ -702,7 +704,7 @@ __device__ __forceinline__ void narrow_controller(const DenseState<T>& s, Narrow
         }
         // ---- publish the round (the queue is compacted to q[0..n) at this point, head == 0) -----
         int parts = 1;
-        while (parts < 4 && n * parts * 2 <= scanners && (s.cols4 + parts * 2 - 1) / (parts * 2) >= 4 * kThreads)
+        while (parts < s.max_parts && n * parts * 2 <= scanners && (s.cols4 + parts * 2 - 1) / (parts * 2) >= 1024)
             parts *= 2;
         TICK_INIT;
         ++seq;

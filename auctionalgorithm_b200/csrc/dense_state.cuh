@@ -90,6 +90,7 @@ template <typename T> struct DenseState
     int min_seg;     // smallest row segment a warp takes when rows are split (multiple of 128)
     int2* cand;      // [rows][kCand] (column, bits of a): edges that were among the row's best, -1: empty
     NarrowCtrl* narrow;
+    int max_parts;   // narrow rounds: at most this many CTAs share one bidder's row (power of two)
     int narrow_rows; // a round with at most this many bidders (and at most SMs - 1) runs as a narrow round
     int tail_rows;   // a round with at most this many bidders is finished by the Gauss-Seidel tail (0: never)
     int dry;         // 1: measurement sweep, bids are computed and stored but not offered

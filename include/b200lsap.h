@@ -68,7 +68,7 @@ typedef struct
     int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
                               of a round, driven from the host (profiling and cross-checks) */
     int32_t tail_rows;     /* a round with at most this many bidders is finished by the Gauss-Seidel
-                              tail on one SM, one bid at a time; 0: default (2), -1: never, at most
+                              tail on one SM, one bid at a time; 0: default (1), -1: never, at most
                               256.  Persistent driver only. */
     int32_t narrow_rows;   /* a round with at most this many bidders (and at most SMs - 1) runs as a
                               narrow round: one CTA per bidder row, a controller CTA instead of grid

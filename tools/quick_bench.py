@@ -49,12 +49,14 @@ if __name__ == "__main__":
         dense(2048, 2048); dense(4096, 4096)
     if "c4d" in which:
         dense(16384, 16384, reps=1)
-        dense(16384, 16384, reps=1, tail_rows=8)
+        dense(16384, 16384, reps=1, tail_rows=-1)
+        dense(16384, 16384, reps=1, tail_rows=1)
     if "c4" in which:
         for opt in (dict(), dict(tail_rows=1), dict(tail_rows=4), dict(tail_rows=8), dict(narrow_rows=-1, tail_rows=8),
                     dict(narrow_rows=-1, tail_rows=-1)):
             dense(16384, 16384, reps=2, **opt)
     if "c4d" in which:
         dense(16384, 16384, reps=1)
-        dense(16384, 16384, reps=1, tail_rows=8)
+        dense(16384, 16384, reps=1, tail_rows=-1)
+        dense(16384, 16384, reps=1, tail_rows=1)
     if "c4" in which: dense(16384, 16384, reps=1)

@@ -53,6 +53,14 @@ SIGNATURES = {
     "b200lsap_generate_shard_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.c_uint64, C.c_uint64]),
     "b200lsap_bid_sweep_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, C.c_int, C.POINTER(C.c_double),
                                                 C.POINTER(_i64)]),
+    "b200lsap_shard_record_bytes": (_i64, []),
+    "b200lsap_shard_begin_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.POINTER(Options),
+                                           C.POINTER(C.c_double)]),
+    "b200lsap_shard_set_amax": (C.c_int, [_H, C.c_double]),
+    "b200lsap_shard_bid": (C.c_int, [_H, _P, C.POINTER(_i64)]),
+    "b200lsap_shard_resolve": (C.c_int, [_H, _P, C.c_int, C.POINTER(_i64)]),
+    "b200lsap_shard_next_phase": (C.c_int, [_H, C.POINTER(C.c_int)]),
+    "b200lsap_shard_finish": (C.c_int, [_H, _P, _P, C.POINTER(Stats)]),
     "b200lsap_debug_counters": (C.c_int, [_H, C.POINTER(_i64), C.c_int]),
     "b200lsap_host_alloc": (C.c_void_p, [_i64]),
     "b200lsap_host_free": (None, [_P]),

@@ -12,6 +12,7 @@
 
 #include "batch_kernels.cuh"
 #include "dense_kernels.cuh"
+#include "shard_kernels.cuh"
 
 using namespace b200lsap;
 
@@ -63,6 +64,17 @@ struct b200lsap_handle
     int min_seg = 512;
     int max_parts = 4;
     int64_t launches = 0;
+    // column-sharded solve in progress (b200lsap_shard_*)
+    struct
+    {
+        bool active = false;
+        const float* A = nullptr;
+        int64_t rows = 0, cols_local = 0, ld = 0, col0 = 0, cols_global = 0;
+        std::vector<double> eps;
+        int phase = 0, cur = 0;
+        int64_t n = 0, rounds = 0, bids = 0, max_rounds = 0;
+        int grid = 0;
+    } sh;
 };
 
 namespace
@@ -846,6 +858,219 @@ int b200lsap_bid_sweep_device_f32(b200lsap_handle* h, const float* a_dev, int64_
     if (bytes_out)
         *bytes_out = rows * cols * (int64_t)sizeof(float);
     return B200LSAP_OK;
+}
+
+} // extern "C"
+
+// =============================================================================================
+// Column-sharded solve: one big problem over several GPUs, one exchange per round.  The caller
+// owns the exchange (an all-gather of the records between shard_bid and shard_resolve).
+// =============================================================================================
+namespace
+{
+
+DenseState<float> shard_state(b200lsap_handle* h, bool scan_view)
+{
+    const auto& sh = h->sh;
+    DenseState<float> s = bind_state<float>(h, sh.A, sh.rows, scan_view ? sh.cols_local : sh.cols_global,
+                                            scan_view ? sh.ld : round_up(sh.cols_global, 32));
+    if (scan_view)
+    {
+        s.prices += sh.col0;
+        s.pricesf += sh.col0;
+    }
+    return s;
+}
+
+int shard_fetch_ctrl(b200lsap_handle* h)
+{
+    CU(cudaMemcpyAsync(h->h_ctrl, h->ctrl.p, 4 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    return B200LSAP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int64_t b200lsap_shard_record_bytes(void) { return (int64_t)sizeof(ShardRec); }
+
+int b200lsap_shard_begin_f32(b200lsap_handle* h, const float* a_dev, int64_t rows, int64_t cols_local, int64_t ld,
+                             int64_t col0, int64_t cols_global, const b200lsap_options* opts, double* amax_local)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (!a_dev || !amax_local)
+        return fail(h, B200LSAP_ERR_ARG, "null pointer");
+    if (rows < 1 || cols_local < 1 || col0 < 0 || col0 + cols_local > cols_global || rows > cols_global ||
+        cols_global > 0x7fff0000ll || ld < round_up(cols_local, 4))
+        return fail(h, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    if (ld % 4 != 0 || col0 % 4 != 0 || ((uintptr_t)a_dev & 15) != 0)
+        return fail(h, B200LSAP_ERR_ARG,
+                    "a shard must be row-major, 16-byte aligned, with ld and col0 multiples of 4 (columns "
+                    "[cols_local, cols_local rounded up to 4) of every row zero)");
+    CU(cudaSetDevice(h->device));
+    DensePlan plan;
+    int rc = make_plan(h, rows, cols_global, opts, plan);
+    if (rc)
+        return rc;
+    auto& sh = h->sh;
+    sh.A = a_dev;
+    sh.rows = rows;
+    sh.cols_local = cols_local;
+    sh.ld = ld;
+    sh.col0 = col0;
+    sh.cols_global = cols_global;
+    sh.eps = plan.eps;
+    sh.phase = 0;
+    sh.cur = 0;
+    sh.n = rows;
+    sh.rounds = sh.bids = 0;
+    sh.max_rounds = plan.max_rounds;
+    rc = persistent_grid<float>(h, sh.grid);
+    if (rc)
+        return rc;
+    rc = alloc_state<float>(h, rows, cols_global, round_up(cols_global, 32), sh.grid * kWarpsPerBlock);
+    if (rc)
+        return rc;
+    h->launches = 0;
+    DenseState<float> g = shard_state(h, false), l = shard_state(h, true);
+    CU(cudaMemsetAsync(g.ctrl, 0, sizeof(DenseCtrl), h->stream));
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_init<float><<<sh.grid, kThreads, 0, h->stream>>>(g, 0);
+    k_absmax<float><<<grid_for(h, rows * (round_up(cols_local, 4) / 4), 256 * 8), 256, 0, h->stream>>>(l.A, l.ld, l.rows, l.cols4,
+                                                                                      l.ctrl);
+    h->launches += 2;
+    CU(cudaMemcpyAsync(h->h_ctrl, g.ctrl, sizeof(DenseCtrl), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    *amax_local = h->h_ctrl->amax;
+    sh.active = true;
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_set_amax(b200lsap_handle* h, double amax_global)
+{
+    if (!h || !h->sh.active)
+        return fail(h, B200LSAP_ERR_ARG, "no sharded solve in progress");
+    CU(cudaSetDevice(h->device));
+    h->h_ctrl->amax = amax_global;
+    CU(cudaMemcpyAsync(&h->ctrl.as<DenseCtrl>()->amax, &h->h_ctrl->amax, sizeof(double), cudaMemcpyHostToDevice,
+                       h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_bid(b200lsap_handle* h, void* rec_dev, int64_t* n_out)
+{
+    if (!h || !h->sh.active)
+        return fail(h, B200LSAP_ERR_ARG, "no sharded solve in progress");
+    if (!rec_dev || !n_out)
+        return fail(h, B200LSAP_ERR_ARG, "null pointer");
+    auto& sh = h->sh;
+    CU(cudaSetDevice(h->device));
+    *n_out = sh.n;
+    if (sh.n == 0)
+        return B200LSAP_OK;
+    if (sh.rounds >= sh.max_rounds)
+        return fail(h, B200LSAP_ERR_MAX_ROUNDS, b200lsap_status_string(B200LSAP_ERR_MAX_ROUNDS));
+    DenseState<float> l = shard_state(h, true);
+    ShardView sv{static_cast<ShardRec*>(rec_dev), (int)sh.col0};
+    k_shard_bid<float><<<sh.grid, kThreads, 0, h->stream>>>(l, sv, sh.cur, (int)sh.n);
+    h->launches++;
+    CU(cudaGetLastError());
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_resolve(b200lsap_handle* h, const void* gathered_dev, int n_ranks, int64_t* n_next)
+{
+    if (!h || !h->sh.active)
+        return fail(h, B200LSAP_ERR_ARG, "no sharded solve in progress");
+    if (!gathered_dev || !n_next || n_ranks < 1)
+        return fail(h, B200LSAP_ERR_ARG, "bad argument");
+    auto& sh = h->sh;
+    CU(cudaSetDevice(h->device));
+    if (sh.n == 0)
+    {
+        *n_next = 0;
+        return B200LSAP_OK;
+    }
+    DenseState<float> g = shard_state(h, false);
+    const int n = (int)sh.n;
+    k_shard_merge<float><<<grid_for(h, n, 256), 256, 0, h->stream>>>(g, static_cast<const ShardRec*>(gathered_dev),
+                                                                   n_ranks, sh.cur, n, sh.eps[sh.phase]);
+    k_resolve<float><<<grid_for(h, n, kThreads), kThreads, 0, h->stream>>>(g, sh.cur, n);
+    k_shard_compact<<<1, 1024, 0, h->stream>>>(g.row2col, g.rows, g.list[sh.cur ^ 1], &g.ctrl->count[sh.cur ^ 1]);
+    h->launches += 3;
+    int rc = shard_fetch_ctrl(h);
+    if (rc)
+        return rc;
+    if (h->h_ctrl->status != 0)
+    {
+        const int st = h->h_ctrl->status;
+        sh.active = false;
+        return fail(h, st == 4 ? B200LSAP_ERR_ARG : st,
+                    st == 4 ? "sharded solve: the ranks' records are not in the same bidder order"
+                            : b200lsap_status_string(st));
+    }
+    sh.rounds++;
+    sh.bids += n;
+    sh.cur ^= 1;
+    sh.n = h->h_ctrl->count[sh.cur];
+    *n_next = sh.n;
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_next_phase(b200lsap_handle* h, int* more)
+{
+    if (!h || !h->sh.active || !more)
+        return fail(h, B200LSAP_ERR_ARG, "no sharded solve in progress");
+    auto& sh = h->sh;
+    CU(cudaSetDevice(h->device));
+    *more = 0;
+    if (sh.n != 0 || sh.phase + 1 >= (int)sh.eps.size())
+        return B200LSAP_OK;
+    sh.phase++;
+    DenseState<float> g = shard_state(h, false);
+    k_reset<float><<<sh.grid, kThreads, 0, h->stream>>>(g, sh.cur);
+    h->launches++;
+    CU(cudaGetLastError());
+    sh.n = sh.rows;
+    *more = 1;
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_finish(b200lsap_handle* h, int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    if (!h || !h->sh.active)
+        return fail(h, B200LSAP_ERR_ARG, "no sharded solve in progress");
+    auto& sh = h->sh;
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    if (row_to_col_dev)
+        CU(cudaMemcpyAsync(row_to_col_dev, h->row2col.p, sh.rows * sizeof(int32_t), cudaMemcpyDeviceToDevice,
+                           h->stream));
+    if (prices_dev)
+        CU(cudaMemcpyAsync(prices_dev, h->prices.p, sh.cols_global * sizeof(double), cudaMemcpyDeviceToDevice,
+                           h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (stats)
+    {
+        memset(stats, 0, sizeof *stats);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+        stats->ms_solve = ms; // includes the caller's exchanges
+        stats->rounds = sh.rounds;
+        stats->bids = sh.bids;
+        stats->phases = sh.phase + 1;
+        stats->bid_bytes = sh.bids * sh.cols_local * (int64_t)sizeof(float);
+        stats->eps_final = sh.eps.back();
+        stats->launches = h->launches;
+    }
+    h->last_cols = sh.cols_global;
+    sh.active = false;
+    return sh.n == 0 ? B200LSAP_OK : fail(h, B200LSAP_ERR_ARG, "sharded solve finished with bidders left");
 }
 
 } // extern "C"

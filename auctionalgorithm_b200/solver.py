@@ -157,6 +157,41 @@ class Handle:
         self._check(self._lib.b200lsap_generate_shard_device_f32(self._h, C.c_void_p(a_ptr), rows, cols_local, ld,
                                                                  col0, cols_global, seed, problem))
 
+    # ---- column-sharded solve (one rank's side; auctionalgorithm_b200/sharded.py drives it) ----
+    def shard_begin(self, a_ptr: int, rows: int, cols_local: int, ld: int, col0: int, cols_global: int,
+                    **options) -> float:
+        o = self._opts(**options)
+        amax = C.c_double(0)
+        self._check(self._lib.b200lsap_shard_begin_f32(self._h, C.c_void_p(a_ptr), rows, cols_local, ld, col0,
+                                                       cols_global, C.byref(o), C.byref(amax)))
+        return amax.value
+
+    def shard_set_amax(self, amax: float):
+        self._check(self._lib.b200lsap_shard_set_amax(self._h, amax))
+
+    def shard_bid(self, rec_ptr: int) -> int:
+        n = C.c_int64(0)
+        self._check(self._lib.b200lsap_shard_bid(self._h, C.c_void_p(rec_ptr), C.byref(n)))
+        return n.value
+
+    def shard_resolve(self, gathered_ptr: int, n_ranks: int) -> int:
+        n = C.c_int64(0)
+        self._check(self._lib.b200lsap_shard_resolve(self._h, C.c_void_p(gathered_ptr), n_ranks, C.byref(n)))
+        return n.value
+
+    def shard_next_phase(self) -> bool:
+        more = C.c_int(0)
+        self._check(self._lib.b200lsap_shard_next_phase(self._h, C.byref(more)))
+        return bool(more.value)
+
+    def shard_finish(self, r2c_ptr: int, prices_ptr: int = 0) -> dict:
+        st = Stats()
+        rc = self._lib.b200lsap_shard_finish(self._h, C.c_void_p(r2c_ptr), C.c_void_p(prices_ptr) if prices_ptr else None,
+                                             C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return self.last_stats
+
     def debug_counters(self):
         out = (C.c_int64 * 16)()
         self._check(self._lib.b200lsap_debug_counters(self._h, out, 16))

@@ -152,6 +152,33 @@ int b200lsap_generate_shard_device_f32(b200lsap_handle* handle, float* a_dev, in
                                        int64_t cols_local, int64_t ld, int64_t col0, int64_t cols_global,
                                        uint64_t seed, uint64_t problem);
 
+/*
+ * Column-sharded solve of ONE big fp32 problem over several GPUs — AuctionMT's decomposition
+ * (column intervals per worker, AuctionMT.h:76-77 and AuctionCommon.h:302-320; exact top-2 merge in
+ * interval order, AuctionMT.h:377-398) with a GPU per interval and one exchange per round.
+ * Every rank holds columns [col0, col0+cols_local) of the matrix (row-major, 16-byte aligned, ld
+ * and col0 multiples of 4, ld >= cols_local rounded up to 4 with the columns in between zero;
+ * ranks in increasing col0 order) and a replica of the prices
+ * and of the assignment.  Per round, on every rank:
+ *     shard_bid      -> n records (b200lsap_shard_record_bytes() each) in rec_dev
+ *     all-gather of the records, rank-major: gathered[r*n + b]      (the caller's: NCCL, NVLink)
+ *     shard_resolve  -> merges, resolves, updates the replica; n_next bidders remain
+ * until n_next == 0; then shard_next_phase (eps scaling, square problems) and, when it reports
+ * no more phases, shard_finish.  begin returns this rank's max |a|; the caller must set the
+ * maximum over all ranks with shard_set_amax before the first bid (it scales the slack of the
+ * single-precision filter).  auctionalgorithm_b200/sharded.py drives this with torch.distributed.
+ */
+int64_t b200lsap_shard_record_bytes(void);
+int b200lsap_shard_begin_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols_local,
+                             int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts,
+                             double* amax_local);
+int b200lsap_shard_set_amax(b200lsap_handle* handle, double amax_global);
+int b200lsap_shard_bid(b200lsap_handle* handle, void* rec_dev, int64_t* n_out);
+int b200lsap_shard_resolve(b200lsap_handle* handle, const void* gathered_dev, int n_ranks, int64_t* n_next);
+int b200lsap_shard_next_phase(b200lsap_handle* handle, int* more);
+int b200lsap_shard_finish(b200lsap_handle* handle, int32_t* row_to_col_dev, double* prices_dev,
+                          b200lsap_stats* stats);
+
 /* Full-sweep bidding pass for measurement: every row bids once against the handle's current
  * prices of the last device solve (or zero prices), nothing is updated.  Returns through
  * ms_out the CUDA-event time of that single kernel; bytes_out = rows*cols*sizeof(float). */

@@ -1,19 +1,23 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark of the B200 auction path (contract: task brief §④).
+"""bench.py — headline benchmark of the B200 auction path (contract: task brief §4).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c2|c3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c4|c2|c1]
 
-Default workload (N = 1): BASELINE.json configs[3] = C4, one dense 16384 x 16384 fp32 problem
-(1 GiB, larger than L2) solved to the reference's assignment.  A step = one full solve.
-  value      solve ms per problem, matrix already resident in HBM (CUDA events on the stream)
-  e2e        the same solve through the reference-facing host API (Eigen-layout column-major
-             pinned host matrix in, row->column out): H2D + transpose + solve + D2H in the timed region
-  roofline   the bidding kernel alone (every row bids once, one launch), measured live
-  cpu_baseline  the CPU oracle port of Auction<double>::solve on a bounded sample of the same input
-  mht        BASELINE's second quantity: batched 32x48 problems/s (C3), sharded over the N GPUs
-N > 1: the dense solve does not shard ("replicas only"): every rank solves its own
-replica and value is the aggregate ms per solve (step time / N); the batched C3 numbers in `mht`
-are the path that shards.
+Default workload: BASELINE.json configs[3] = C4, the configuration the metric is quoted on: one dense
+16384 x 16384 fp32 problem (1 GiB, larger than L2) solved to the reference's assignment.  A step = one
+full solve.
+  value         solve ms per problem, matrix already resident in HBM (CUDA events on the stream)
+  e2e           the same solve through the reference-facing host API (Eigen-layout column-major pinned
+                host matrix in, row->column out): H2D + transpose + solve + D2H inside the timed region
+  roofline      the bidding kernel alone (every row bids once, one launch), timed live with CUDA events
+  cpu_baseline  the CPU port of Auction<double>::solve (oracle/, pinned bit-for-bit against the compiled
+                reference) on a bounded sample of the same input, scaled by the reference's bid count
+  mht           BASELINE's second quantity: batched 32x48 problems/s (C3), sharded over the N ranks
+  sharded       BASELINE configs[4]: 65536 x 98304 column-sharded over the N ranks, one all-gather of
+                32-byte records per round (N = 1: the same code path with a single shard)
+N > 1: a single mid-size dense problem does not shard ("replicas only"): every rank solves
+its own replica and `value` is the aggregate ms per solve (step time / N); `mht` and `sharded` are the
+paths that shard.
 """
 from __future__ import annotations
 
@@ -32,6 +36,7 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     "c1": dict(rows=200, cols=300), "c2": dict(rows=2048, cols=3072), "c4": dict(rows=16384, cols=16384),
 }
+C5 = dict(rows=65536, cols=98304)
 SEED = 1
 
 
@@ -80,68 +85,103 @@ def peaks() -> tuple[float, str]:
         return 6650.0, "fallback"
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of the bidding kernel from the committed ncu --set full summary."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "kbid_ncu_summary.json")))["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def c4_reference_counters() -> dict:
     p = os.path.join(ROOT, "tests", "golden", "c4_oracle_stats.json")
     return json.load(open(p)) if os.path.exists(p) else {}
 
 
-def cpu_sample(rows: int, cols: int, seconds_target: float = 12.0) -> dict:
-    """Times the CPU oracle port (oracle/auction_oracle.c = Auction<double>::solve restated, pinned
-    bit-for-bit against the compiled reference) on a bounded sample of the workload and scales it
-    to a whole solve.  Small workloads run to completion; C4 runs a bid budget and is scaled by the
-    reference's total bid count recorded in tests/golden/c4_oracle_stats.json."""
-    import numpy as np
-    from oracle import pyoracle as po
-    po.build()
-    a = np.asfortranarray(po.generate(rows, cols, SEED).astype(np.float64))  # Eigen layout, widened fp32
-    full = rows * cols <= 4096 * 6144 and rows != cols
-    if full:
+class CpuArm:
+    """The reference's CPU path on the host cores.  Auction<Scalar>::solve is single-threaded by
+    construction (Auction.h:44-109); AuctionMT is timed beside it on a small case because it is slower
+    than the single thread at every size (two barrier crossings per bid)."""
+
+    def __init__(self, rows: int, cols: int):
+        import numpy as np
+        from oracle import pyoracle as po
+        po.build()
+        self.po, self.np, self.rows, self.cols = po, np, rows, cols
+        self.a = np.asfortranarray(po.generate(rows, cols, SEED).astype(np.float64))  # Eigen layout, widened fp32
+        self.full = rows * cols <= 4096 * 6144 and rows != cols
+        self.budget = None
+
+    def sample(self, seconds_target: float) -> dict:
+        po, a, rows, cols = self.po, self.a, self.rows, self.cols
+        if self.full:
+            if po.reference() is not None:
+                out = po.reference_solve(a, "auction")
+                return dict(value=out["seconds"] * 1e3, unit="ms", cores=1, kind="reference",
+                            sample=f"full Auction<double>::solve of {rows}x{cols} seed {SEED} (unmodified reference headers)")
+            t = time.perf_counter()
+            out = po.oracle_solve(a)
+            sec = time.perf_counter() - t
+            return dict(value=sec * 1e3, unit="ms", cores=1, kind="port",
+                        sample=f"full Auction<double> solve of {rows}x{cols} seed {SEED}: {out['stats']['bids']} bids")
+        if self.budget is None:
+            po.oracle_solve(a, max_bids=1000)
+            t = time.perf_counter()
+            probe = po.oracle_solve(a, max_bids=3000)
+            per_bid = (time.perf_counter() - t) / max(probe["stats"]["bids"], 1)
+            self.budget = max(3000, int(seconds_target / per_bid))
         t = time.perf_counter()
-        out = po.oracle_solve(a)
+        out = po.oracle_solve(a, max_bids=self.budget)
         sec = time.perf_counter() - t
-        return dict(value=sec * 1e3, unit="ms", cores=1, kind="port",
-                    sample=f"full Auction<double> solve of {rows}x{cols} seed {SEED}: {out['stats']['bids']} bids")
-    probe = po.oracle_solve(a, max_bids=2000)
-    t = time.perf_counter()
-    probe = po.oracle_solve(a, max_bids=4000)
-    per_bid = (time.perf_counter() - t) / max(probe["stats"]["bids"], 1)
-    budget = max(4000, int(seconds_target / per_bid))
-    t = time.perf_counter()
-    out = po.oracle_solve(a, max_bids=budget)
-    sec = time.perf_counter() - t
-    bids = out["stats"]["bids"]
-    ref = c4_reference_counters() if (rows, cols) == (16384, 16384) else {}
-    if out["status"] == po.ORC_OK:
-        return dict(value=sec * 1e3, unit="ms", cores=1, kind="port", sample=f"full solve, {bids} bids")
-    if ref.get("bids"):
-        total = ref["bids"]
-        note = (f"first {bids} bids of Auction<double> on {rows}x{cols} seed {SEED} took {sec:.1f} s "
-                f"({1e6 * sec / bids:.0f} us/bid); scaled to the {total} bids of the full reference solve "
-                f"(measured offline: {ref.get('seconds_reference', 0):.0f} s, tests/golden/c4_oracle_stats.json)")
-        return dict(value=sec / bids * total * 1e3, unit="ms", cores=1, kind="port", sample=note)
-    return dict(value=None, unit="ms", cores=1, kind="port",
-                sample=f"first {bids} bids took {sec:.1f} s ({1e6 * sec / bids:.0f} us/bid); total bid count unknown")
+        bids = out["stats"]["bids"]
+        if out["status"] == po.ORC_OK:
+            return dict(value=sec * 1e3, unit="ms", cores=1, kind="port", sample=f"full solve, {bids} bids")
+        ref = c4_reference_counters() if (rows, cols) == (16384, 16384) else {}
+        if ref.get("bids"):
+            total = ref["bids"]
+            note = (f"first {bids} bids of Auction<double> (CPU port, bit-identical to the reference) on {rows}x{cols} "
+                    f"seed {SEED} took {sec:.1f} s ({1e6 * sec / bids:.0f} us/bid), scaled to the {total} bids of the "
+                    f"full reference solve; the unmodified reference measured offline took "
+                    f"{ref.get('seconds_reference', 0):.0f} s (tests/golden/c4_oracle_stats.json)")
+            return dict(value=sec / bids * total * 1e3, unit="ms", cores=1, kind="port", sample=note)
+        return dict(value=None, unit="ms", cores=1, kind="port",
+                    sample=f"first {bids} bids took {sec:.1f} s ({1e6 * sec / bids:.0f} us/bid); total bid count unknown")
+
+    def mt_note(self) -> dict:
+        """AuctionMT (ThreadBarrier) beside Auction on a bounded square case, unmodified reference."""
+        po, np = self.po, self.np
+        if po.reference() is None:
+            return {"unavailable": "oracle/_ref not built"}
+        n = 1024
+        a = np.asfortranarray(po.generate(n, n, SEED).astype(np.float64))
+        st = po.reference_solve(a, "auction")["seconds"]
+        cores = os.cpu_count() or 1
+        out = {"case": f"{n}x{n} double, seed {SEED}", "auction_st_ms": st * 1e3, "host_cores": cores}
+        for t in sorted({2, min(4, cores)}):
+            out[f"auctionmt_{t}threads_ms"] = po.reference_solve(a, "mt", n_threads=t)["seconds"] * 1e3
+        return out
 
 
 def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
     w = WORKLOADS[args.workload]
+    arm = CpuArm(w["rows"], w["cols"])
     vals, last = [], None
     for k in range(args.warmup + args.steps):
-        last = cpu_sample(w["rows"], w["cols"], seconds_target=8.0)
+        last = arm.sample(seconds_target=6.0)
         if k >= args.warmup and last["value"] is not None:
             vals.append(last["value"])
     v = statistics.mean(vals) if vals else None
-    last["value"] = v
+    last = dict(last, value=v)
     print(json.dumps({
         "impl": "reference", "metric": f"solve_ms_{w['rows']}x{w['cols']}_fp32", "value": v, "unit": "ms",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": v,
         "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{args.workload}: dense {w['rows']}x{w['cols']} fp32 widened to f64, seed {SEED}, "
-                               "reference Auction<double>::solve on the host, single thread"},
-        "cpu_baseline": last,
+                               "the reference's Auction<double>::solve on the host, single thread (the solver is "
+                               "single-threaded; AuctionMT is slower at every size, see cpu_baseline.auctionmt)"},
+        "cpu_baseline": dict(last, auctionmt=arm.mt_note()),
         "e2e": {"value": v, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -165,6 +205,43 @@ def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int):
     return ms, st["bid_bytes"]
 
 
+def run_sharded(handle, torch, dist, rank: int, world: int, steps: int, rows: int, cols: int):
+    """C5: one rows x cols problem column-sharded over the ranks, generated per shard on the device."""
+    from auctionalgorithm_b200 import sharded
+    c0, cl = sharded.split_columns(cols, world)[rank]
+    t = torch.empty((rows, cl), dtype=torch.float32, device="cuda")
+    handle.generate_shard_device(t.data_ptr(), rows, cl, cl, c0, cols, SEED)
+    eng = sharded.CudaShardEngine(handle, t, rows, cl, cl, c0, cols)
+
+    def once():
+        if world > 1:
+            return sharded.solve_sharded(eng, rows)
+        return sharded.solve_sharded_emulated([eng], rows)[0]
+
+    once()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        r2c, _, st = once()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        tt = torch.tensor([ms], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    r2c = r2c.cpu().numpy()
+    ok = bool((r2c >= 0).all() and len(set(r2c.tolist())) == rows)
+    return {"workload": f"c5: dense {rows}x{cols} fp32 column-sharded over {world} rank(s), seed {SEED}, device-generated",
+            "ms_per_solve": ms, "rounds": st["rounds"], "bids": st["bids"],
+            "bid_gbs_all_ranks": st["bids"] * cols * 4 / ms / 1e6,
+            "exchange": "all-gather of 32-byte records per round (NCCL)" if world > 1 else "none (single shard)",
+            "exchanged_bytes_per_solve": st.get("exchanged_bytes", 0), "one_to_one_assignment": ok}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -174,7 +251,10 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the column-sharded C5 leg")
     ap.add_argument("--mht-problems", type=int, default=1 << 20, help="C3 problems per GPU")
+    ap.add_argument("--c5-rows", type=int, default=C5["rows"])
+    ap.add_argument("--c5-cols", type=int, default=C5["cols"])
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -202,6 +282,13 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        tt = torch.tensor([x], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
     # ---- device-resident solve --------------------------------------------------------------
     a_dev = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
     r2c_dev = torch.empty(rows, dtype=torch.int32, device="cuda")
@@ -221,11 +308,7 @@ def main():
     e1.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    ms_step = e0.elapsed_time(e1) / args.steps
-    if world > 1:
-        tt = torch.tensor([ms_step], device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_step = float(tt.item())
+    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     solve_stats = st
 
     # ---- parity of what was just timed (rank 0, against the reference-made golden vector) ------
@@ -244,9 +327,9 @@ def main():
         sweep_ms.append(ms)
     sweep = statistics.mean(sweep_ms[3:])
     peak, peak_src = peaks()
-    roofline = {"bound": "hbm", "kernel": "k_bid<float> (bidding phase, every row bids once)",
+    roofline = {"bound": "hbm", "kernel": "k_bid<float> (bidding phase of a wide round, every row bids once)",
                 "achieved": nbytes / sweep / 1e6, "peak": peak, "unit": "GB/s",
-                "frac": nbytes / sweep / 1e6 / peak, "traffic": None, "peak_source": peak_src,
+                "frac": nbytes / sweep / 1e6 / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
                 "ms_per_launch": sweep, "algorithmic_bytes_per_launch": nbytes}
     solve_gbs = solve_stats["bid_bytes"] / (ms_step * 1e6)
 
@@ -262,18 +345,13 @@ def main():
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            r2c_host = handle.solve(a_host)
+            handle.solve(a_host)
         torch.cuda.synchronize()
-        e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-        if world > 1:
-            tt = torch.tensor([e2e_ms], device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            e2e_ms = float(tt.item())
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
         e2e = {"value": e2e_ms / world, "unit": "ms", "h2d_bytes_per_step": rows * cols * 4,
                "d2h_bytes_per_step": rows * 8, "ms_upload": handle.last_stats["ms_upload"],
                "ms_solve": handle.last_stats["ms_solve"], "ms_download": handle.last_stats["ms_download"],
                "input": "pinned host, column-major (Eigen default)"}
-        launches_e2e = handle.last_stats["launches"]
         del host, a_host
     else:
         del a_dev
@@ -281,35 +359,45 @@ def main():
 
     # ---- C3: batched 32x48 problems, sharded over ranks, no collective -------------------------
     mht_ms, mht_bytes = run_mht(handle, torch, args.mht_problems, rank, max(args.steps, 3), 3)
-    if world > 1:
-        tt = torch.tensor([mht_ms], device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        mht_ms = float(tt.item())
+    mht_ms = max_over_ranks(mht_ms)
     mht = {"problems_per_s": args.mht_problems * world / (mht_ms * 1e-3), "problems": args.mht_problems * world,
-           "ms_per_step": mht_ms, "gbs_per_gpu": mht_bytes / mht_ms / 1e6, "frac_of_hbm_peak": mht_bytes / mht_ms / 1e6 / peak,
-           "layout": "row-major 32x48 fp32 problems, device-generated, resident in HBM"}
+           "ms_per_step": mht_ms, "gbs_per_gpu": mht_bytes / mht_ms / 1e6,
+           "frac_of_hbm_peak": mht_bytes / mht_ms / 1e6 / peak,
+           "layout": "row-major 32x48 fp32 problems, device-generated, resident in HBM; one shard per rank"}
+    torch.cuda.empty_cache()
+
+    # ---- C5: column-sharded big problem ------------------------------------------------------------
+    shard = None
+    if not args.no_sharded:
+        shard = run_sharded(handle, torch, dist, rank, world, 2, args.c5_rows, args.c5_cols)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_sample(rows, cols)
+        arm = CpuArm(rows, cols)
+        cpu = arm.sample(12.0)
+        cpu["auctionmt"] = arm.mt_note()
 
     if rank == 0:
+        big = rows * cols * 4 > 126e6
         print(json.dumps({
             "metric": f"solve_ms_{rows}x{cols}_fp32", "value": ms_step / world, "unit": "ms", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: dense {rows}x{cols} fp32 (BASELINE.json configs), uniform grid "
-                                   f"(0,1], seed {SEED}, device-generated; inputs larger than L2" if rows * cols * 4 > 126e6
-                       else f"{args.workload}: dense {rows}x{cols} fp32, seed {SEED} (L2-resident)",
-                       "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (dense solve does not shard)",
+            "config": {"workload": (f"{args.workload}: dense {rows}x{cols} fp32 (BASELINE.json configs), uniform grid "
+                                    f"(0,1], seed {SEED}, device-generated; "
+                                    + ("inputs larger than L2" if big else "L2-resident")),
+                       "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (a mid-size dense solve does not shard)",
                        "eps_final": solve_stats["eps_final"], "rounds": solve_stats["rounds"], "bids": solve_stats["bids"],
-                       "phases": solve_stats["phases"], "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"], 1),
+                       "phases": solve_stats["phases"], "narrow_rounds": solve_stats["narrow_rounds"],
+                       "tail_bids": solve_stats["tail_bids"],
+                       "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"] + solve_stats["tail_bids"], 1),
                        "parity_vs_reference_golden": parity_note},
             "roofline": roofline,
             "solve_algorithmic_gbs": solve_gbs,
             "cpu_baseline": cpu,
             "e2e": e2e,
             "mht": mht,
+            "sharded": shard,
             "gpu_launches": launches,
             "clocks": clocks,
         }))

@@ -678,18 +678,23 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     P.status = &h->ctrl.as<DenseCtrl>()->status;
     CU(cudaMemsetAsync(P.status, 0, sizeof(int), h->stream));
     const int n_pad = (rows * cols + 3) & ~3;
-    const size_t smem = (size_t)kBatchWarps * n_pad * sizeof(float);
-    CU(cudaFuncSetAttribute(k_auction_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = (size_t)kBatchPerWarp * n_pad * sizeof(float);
+    using BatchKernel = void (*)(BatchParams);
+    static const BatchKernel kernels[kBatchColsPerLane] = {k_auction_batch<1>, k_auction_batch<2>, k_auction_batch<3>,
+                                                          k_auction_batch<4>, k_auction_batch<5>, k_auction_batch<6>,
+                                                          k_auction_batch<7>, k_auction_batch<8>};
+    const BatchKernel kernel = kernels[(cols + kBatchGroup - 1) / kBatchGroup - 1];
+    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_auction_batch, kBatchWarps * 32, smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32, smem));
     if (per_sm < 1)
         return fail(h, B200LSAP_ERR_SHAPE, "batched problem does not fit in shared memory");
-    int64_t grid = (batch + kBatchWarps - 1) / kBatchWarps;
+    int64_t grid = (batch + kBatchPerWarp - 1) / kBatchPerWarp;
     const int64_t resident = (int64_t)per_sm * h->num_sms;
     if (grid > resident)
         grid = resident;
     CU(cudaEventRecord(h->ev[1], h->stream));
-    k_auction_batch<<<(int)grid, kBatchWarps * 32, smem, h->stream>>>(P);
+    kernel<<<(int)grid, 32, smem, h->stream>>>(P);
     h->launches++;
     CU(cudaEventRecord(h->ev[2], h->stream));
     CU(cudaMemcpyAsync(&h->h_ctrl->status, P.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));

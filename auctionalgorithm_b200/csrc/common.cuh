@@ -102,6 +102,36 @@ template <typename T> __device__ __forceinline__ void top2_push(Top2<T>& t, T a,
     t.a = gv ? a : t.a;
 }
 
+// Exact float -> double widening on the integer pipe.  cvt.f64.f32 runs on the quarter-rate
+// conversion unit, which saturates long before anything else when every element of a small
+// problem is widened for every bid (ncu: XU pipe > 100 % busy in the batched kernel).  A normal
+// finite float widens by re-biasing the exponent (+896) and shifting the mantissa by 29 bits;
+// zeros, denormals, infinities and NaNs take the conversion instruction out of line.
+__device__ __noinline__ double widen_slow(float a) { return (double)a; }
+
+__device__ __forceinline__ double widen_exact(float a)
+{
+    const unsigned u = __float_as_uint(a);
+    if ((u << 1) - 0x01000000u >= 0xFE000000u)
+        return widen_slow(a);
+    const unsigned hi = (u & 0x80000000u) | (((u & 0x7FFFFFFFu) >> 3) + 0x38000000u);
+    return __hiloint2double((int)hi, (int)(u << 29));
+}
+
+// top2_push for fp32 coefficients with the widening done on the integer pipe (bit-identical).
+__device__ __forceinline__ void top2_push_w(Top2<float>& t, float a, double p, int col)
+{
+    if (a == 0.f)
+        return;
+    const double d = widen_exact(a) - p;
+    const bool gv = d > t.v;
+    const bool gw = d > t.w;
+    t.w = gv ? t.v : (gw ? d : t.w);
+    t.v = gv ? d : t.v;
+    t.j = gv ? col : t.j;
+    t.a = gv ? a : t.a;
+}
+
 template <typename T> __device__ __forceinline__ void top2_merge(Top2<T>& t, const Top2<T>& o)
 {
     const bool other = o.v > t.v || (o.v == t.v && o.j < t.j && o.j >= 0);

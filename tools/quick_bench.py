@@ -39,6 +39,7 @@ if __name__ == "__main__":
     if "c1" in which: dense(200, 300)
     if "c2" in which: dense(2048, 3072)
     if "c3" in which: batch(1 << 16); batch(1 << 20)
+    if "c3s" in which: batch(1 << 18)
     if "sweep" in which:
         t = torch.empty((16384, 16384), dtype=torch.float32, device="cuda")
         h.generate_device(t.data_ptr(), 1, 16384, 16384, 16384, 1, 1)

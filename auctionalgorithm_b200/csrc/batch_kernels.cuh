@@ -46,7 +46,11 @@ template <int kCpl> __global__ void __launch_bounds__(32) k_auction_batch(BatchP
     const int g = lane / kBatchGroup, gl = lane % kBatchGroup;
     const int n = P.rows * P.cols;
     const int n_pad = (n + 3) & ~3;
-    const float* sA = smem + (size_t)g * n_pad;
+    // problem g starts 8 g floats later than dense packing would put it: with a row stride of 48
+    // floats the four groups then read disjoint 8-bank windows whenever their rows have the same
+    // parity (ncu: 70 % of the shared-load wavefronts were bank conflicts without it)
+    const int p_stride = n_pad + kBatchGroup;
+    const float* sA = smem + (size_t)g * p_stride;
     const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
 
     for (long long base = (long long)blockIdx.x * kBatchPerWarp; base < P.batch;
@@ -56,16 +60,17 @@ template <int kCpl> __global__ void __launch_bounds__(32) k_auction_batch(BatchP
         const float* gsrc = P.a + base * n;
         if ((n & 3) == 0)
         {
-            // the four problems are contiguous in HBM and in shared memory: one streaming copy
-            const int vecs = count * n / 4;
-            for (int k = lane; k < vecs; k += 32)
-                reinterpret_cast<float4*>(smem)[k] = ld_stream4(gsrc + 4 * k);
+            // the four problems are contiguous in HBM: streaming 128-bit copies
+            const int vecs = n / 4;
+            for (int q = 0; q < count; q++)
+                for (int k = lane; k < vecs; k += 32)
+                    reinterpret_cast<float4*>(smem + (size_t)q * p_stride)[k] = ld_stream4(gsrc + (size_t)q * n + 4 * k);
         }
         else
         {
             for (int q = 0; q < count; q++)
                 for (int k = lane; k < n; k += 32)
-                    smem[(size_t)q * n_pad + k] = __ldg(gsrc + (size_t)q * n + k);
+                    smem[(size_t)q * p_stride + k] = __ldg(gsrc + (size_t)q * n + k);
         }
         __syncwarp();
 

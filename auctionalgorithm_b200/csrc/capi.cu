@@ -678,7 +678,7 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     P.status = &h->ctrl.as<DenseCtrl>()->status;
     CU(cudaMemsetAsync(P.status, 0, sizeof(int), h->stream));
     const int n_pad = (rows * cols + 3) & ~3;
-    const size_t smem = (size_t)kBatchPerWarp * n_pad * sizeof(float);
+    const size_t smem = (size_t)kBatchPerWarp * (n_pad + kBatchGroup) * sizeof(float);
     using BatchKernel = void (*)(BatchParams);
     static const BatchKernel kernels[kBatchColsPerLane] = {k_auction_batch<1>, k_auction_batch<2>, k_auction_batch<3>,
                                                           k_auction_batch<4>, k_auction_batch<5>, k_auction_batch<6>,

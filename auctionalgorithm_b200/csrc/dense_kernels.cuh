@@ -186,20 +186,27 @@ __device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* _
     warp_top2f(hi, lo);
     const float thr = fmaxf(st.thr, __fsub_rd(lo, margin));
     st.thr = thr;
+    // about two elements of the whole warp survive: a warp-uniform branch per piece keeps the
+    // sixteen exact updates out of the instruction stream unless some lane needs one
 #pragma unroll
     for (int u = 0; u < U; u++)
     {
         const int cc = first + u * stride;
+        float4 f = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
         if (cc < c1)
         {
             const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
-            if (a[u].x - q.x > thr)
+            f = make_float4(a[u].x - q.x, a[u].y - q.y, a[u].z - q.z, a[u].w - q.w);
+        }
+        if (__any_sync(kFullMask, fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > thr))
+        {
+            if (f.x > thr)
                 top2_push(st.t, a[u].x, prices[cc], cc);
-            if (a[u].y - q.y > thr)
+            if (f.y > thr)
                 top2_push(st.t, a[u].y, prices[cc + 1], cc + 1);
-            if (a[u].z - q.z > thr)
+            if (f.z > thr)
                 top2_push(st.t, a[u].z, prices[cc + 2], cc + 2);
-            if (a[u].w - q.w > thr)
+            if (f.w > thr)
                 top2_push(st.t, a[u].w, prices[cc + 3], cc + 3);
         }
     }

@@ -147,40 +147,43 @@ __global__ void __launch_bounds__(256) k_shard_merge(DenseState<T> s, const Shar
     }
 }
 
-// Next round's bidders: unassigned rows in increasing row order (one CTA, block-wide prefix sum).
+// Next round's bidders: unassigned rows in increasing row order.  One CTA; thread t owns the
+// contiguous rows [t * chunk, (t + 1) * chunk), counts, a block-wide exclusive scan of the 1024
+// counts gives its output offset, then it writes its rows in order.
 __global__ void __launch_bounds__(1024) k_shard_compact(const int* __restrict__ row2col, int rows, int* __restrict__ list,
                                                         int* count)
 {
     __shared__ int warp_sum[32];
-    __shared__ int carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0)
-        carry = 0;
-    __syncthreads();
-    for (int base = 0; base < rows; base += 1024)
+    const int chunk = (rows + 1023) / 1024;
+    const int r0 = min(tid * chunk, rows), r1 = min(r0 + chunk, rows);
+    int mine = 0;
+    for (int i = r0; i < r1; i++)
+        mine += row2col[i] < 0;
+    int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1)
     {
-        const int i = base + tid;
-        const bool un = i < rows && row2col[i] < 0;
-        const unsigned m = __ballot_sync(kFullMask, un);
-        if (lane == 0)
-            warp_sum[warp] = __popc(m);
-        __syncthreads();
-        int before = carry, total = 0;
-        for (int k = 0; k < 32; k++)
-        {
-            const int c = warp_sum[k];
-            before += k < warp ? c : 0;
-            total += c;
-        }
-        if (un)
-            list[before + __popc(m & ((1u << lane) - 1))] = i;
-        __syncthreads();
-        if (tid == 0)
-            carry += total;
-        __syncthreads();
+        const int o = __shfl_up_sync(kFullMask, incl, d);
+        if (lane >= d)
+            incl += o;
     }
+    if (lane == 31)
+        warp_sum[warp] = incl;
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int k = 0; k < 32; k++)
+    {
+        const int c = warp_sum[k];
+        before += k < warp ? c : 0;
+        total += c;
+    }
+    int out = before + incl - mine;
+    for (int i = r0; i < r1; i++)
+        if (row2col[i] < 0)
+            list[out++] = i;
     if (tid == 0)
-        *count = carry;
+        *count = total;
 }
 
 } // namespace b200lsap

@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libb200lsap.so")
+# B200LSAP_LIB: another build of the same library (e.g. the -DB200LSAP_TIMING developer build)
+LIB_PATH = os.environ.get("B200LSAP_LIB") or os.path.join(PKG, "libb200lsap.so")
 
 COL_MAJOR, ROW_MAJOR = 0, 1
 OK, ERR_SHAPE, ERR_INFEASIBLE, ERR_MAX_ROUNDS, ERR_CUDA, ERR_ARG, ERR_NO_DEVICE = range(7)
@@ -15,14 +16,15 @@ OK, ERR_SHAPE, ERR_INFEASIBLE, ERR_MAX_ROUNDS, ERR_CUDA, ERR_ARG, ERR_NO_DEVICE 
 class Options(C.Structure):
     _fields_ = [("eps_multiplier", C.c_double), ("eps_scaling", C.c_int32), ("eps_start", C.c_double),
                 ("eps_factor", C.c_double), ("max_rounds", C.c_int64), ("driver", C.c_int32),
-                ("tail_rows", C.c_int32), ("narrow_rows", C.c_int32), ("reserved", C.c_int32)]
+                ("tail_rows", C.c_int32), ("narrow_rows", C.c_int32), ("row_cache", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [("rounds", C.c_int64), ("bids", C.c_int64), ("phases", C.c_int64), ("bid_bytes", C.c_int64),
                 ("eps_final", C.c_double), ("ms_upload", C.c_double), ("ms_solve", C.c_double),
                 ("ms_download", C.c_double), ("launches", C.c_int64), ("tail_bids", C.c_int64), ("tail_runs", C.c_int64),
-                ("narrow_rounds", C.c_int64), ("reserved", C.c_int64 * 1)]
+                ("narrow_rounds", C.c_int64), ("cache_hits", C.c_int64), ("cache_misses", C.c_int64),
+                ("eps_first", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}

@@ -42,6 +42,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     if os.environ.get("B200LSAP_TIMING"):
         cmd.insert(1, "-DB200LSAP_TIMING")
+    if os.environ.get("B200LSAP_VAR"):  # developer experiments (dense_cache.cuh)
+        cmd.insert(1, "-DB200LSAP_VAR=" + os.environ["B200LSAP_VAR"])
+    if os.environ.get("B200LSAP_OUT"):
+        cmd[cmd.index("-o") + 1] = os.environ["B200LSAP_OUT"]
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
         print(" ".join(cmd))

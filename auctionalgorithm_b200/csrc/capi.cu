@@ -56,7 +56,7 @@ struct b200lsap_handle
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;
-    DevBuf a, staging, prices, pricesf, cand, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
+    DevBuf a, staging, prices, pricesf, cand, cache, cache_hdr, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
         ctrl, out64, batch_in, batch_out;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -264,6 +264,9 @@ struct DensePlan
     int driver;
     int tail_rows;
     int narrow_rows;
+    bool eps_auto;     // first eps of the scaling schedule from the data (k_probe / k_schedule; fp32 only)
+    double eps_factor;
+    int use_cache;
 };
 
 // eps schedule (the controller constants of Auction.h:54-55, plus optional scaling).
@@ -282,10 +285,13 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
                     "eps scaling needs rows == cols: a forward-only auction with scaled eps is not optimal on "
                     "asymmetric problems (SURVEY.md section 7.3)");
     plan.eps.clear();
+    plan.eps_auto = scaling && !(o.eps_start > 0);
+    plan.eps_factor = o.eps_factor > 1 ? o.eps_factor : 5.0;
+    plan.use_cache = o.row_cache >= 0;
     if (scaling)
     {
         double e = o.eps_start > 0 ? o.eps_start : 0.25;
-        const double f = o.eps_factor > 1 ? o.eps_factor : 5.0;
+        const double f = plan.eps_factor;
         while (e > eps_final * 1.0000001 && (int)plan.eps.size() < kMaxPhases - 1)
         {
             plan.eps.push_back(e);
@@ -309,6 +315,11 @@ template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t 
     CU(h->prices.ensure((ldp + 512) * sizeof(double)));
     CU(h->pricesf.ensure((ldp + 512) * sizeof(float)));
     CU(h->cand.ensure((size_t)rows * kCand * sizeof(int2)));
+    if (sizeof(T) == 4)
+    {
+        CU(h->cache.ensure((size_t)rows * kCacheK * sizeof(int2)));
+        CU(h->cache_hdr.ensure((size_t)rows * sizeof(RowCacheHdr)));
+    }
     CU(h->narrow.ensure(sizeof(NarrowCtrl)));
     CU(h->profits.ensure(rows * sizeof(double)));
     CU(h->slots.ensure(cols * sizeof(BidSlot)));
@@ -335,6 +346,9 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.prices = h->prices.as<double>();
     s.pricesf = h->pricesf.as<float>();
     s.cand = h->cand.as<int2>();
+    s.cache = sizeof(T) == 4 ? h->cache.as<int2>() : nullptr;
+    s.cache_hdr = sizeof(T) == 4 ? h->cache_hdr.as<RowCacheHdr>() : nullptr;
+    s.use_cache = 0;
     s.narrow = h->narrow.as<NarrowCtrl>();
     s.narrow_rows = 0;
     s.max_parts = h->max_parts;
@@ -389,13 +403,36 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->max_rounds = plan.max_rounds;
     for (size_t k = 0; k < plan.eps.size(); k++)
         hc->eps[k] = plan.eps[k];
+    const bool eps_auto = plan.eps_auto && sizeof(T) == 4;
+    hc->eps_auto = eps_auto ? 1 : 0;
+    hc->eps_factor = plan.eps_factor;
+    hc->eps_final = plan.eps.back();
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
+    s.use_cache = (sizeof(T) == 4 && plan.driver == 0 && plan.use_cache) ? 1 : 0;
+    std::vector<double> eps = plan.eps;
 
     CU(cudaEventRecord(h->ev[1], h->stream));
     k_init<T><<<grid, kThreads, 0, h->stream>>>(s, 0);
     k_absmax<T><<<grid_for(h, plan.rows * (int64_t)(s.cols4 / 4), 256 * 8), 256, 0, h->stream>>>(s.A, s.ld, s.rows, s.cols4,
                                                                                          s.ctrl);
     h->launches += 2;
+    if constexpr (sizeof(T) == 4)
+    {
+        if (eps_auto)
+        {
+            // first eps of the schedule from the data (dense_cache.cuh)
+            const int n_probe = (int)std::min<int64_t>(kProbeRows, plan.rows);
+            k_probe<<<n_probe, kThreads, 0, h->stream>>>(s);
+            k_schedule<<<1, 32, 0, h->stream>>>(s.ctrl, n_probe);
+            h->launches += 2;
+            if (plan.driver != 0)
+            {
+                CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
+                CU(cudaStreamSynchronize(h->stream));
+                eps.assign(hc->eps, hc->eps + hc->n_phases);
+            }
+        }
+    }
     if (plan.driver == 0)
     {
         void* args[] = {&s};
@@ -420,7 +457,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
                 break;
             if (n == 0)
             {
-                if (phase + 1 >= (int)plan.eps.size())
+                if (phase + 1 >= (int)eps.size())
                     break;
                 phase++;
                 k_reset<T><<<grid, kThreads, 0, h->stream>>>(s, cur);
@@ -432,7 +469,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
                 hc->status = B200LSAP_ERR_MAX_ROUNDS;
                 break;
             }
-            k_bid<T><<<grid, kThreads, 0, h->stream>>>(s, cur, n, plan.eps[phase]);
+            k_bid<T><<<grid, kThreads, 0, h->stream>>>(s, cur, n, eps[phase]);
             k_resolve<T><<<grid, kThreads, 0, h->stream>>>(s, cur, n);
             h->launches += 2;
             cur ^= 1;
@@ -444,7 +481,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         hc->rounds = rounds;
         hc->bids = bids;
         hc->gs_bids = hc->gs_episodes = hc->narrow_rounds = 0;
+        hc->cache_hits = hc->cache_misses = 0;
         hc->phase = phase;
+        hc->eps[0] = eps[0];
     }
     CU(cudaGetLastError());
     h->last_cols = plan.cols;
@@ -461,6 +500,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         stats->tail_runs = hc->gs_episodes;
         stats->bid_bytes = hc->bids * plan.cols * (int64_t)sizeof(T);
         stats->eps_final = plan.eps.back();
+        stats->eps_first = hc->eps[0];
+        stats->cache_hits = hc->cache_hits;
+        stats->cache_misses = hc->cache_misses;
     }
     if (hc->status != 0)
         return fail(h, hc->status, b200lsap_status_string(hc->status));

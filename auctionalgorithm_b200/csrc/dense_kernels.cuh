@@ -482,14 +482,37 @@ __device__ __forceinline__ void prefetch_row_l2(const void* row, unsigned bytes)
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(row), "r"(bytes) : "memory");
 }
 
+// Loop invariants of the cached controller, kept in shared memory and re-read where they are used:
+// at 64 registers per thread anything held across the round loop is spilled to the stack, and a
+// stack line that takes one spill store per round costs an L2 round trip at every reload.
+struct NarrowInvariants
+{
+    const int2* cache;
+    const RowCacheHdr* hdr;
+    double* prices;
+    float* pricesf;
+    double* profits;
+    int* owner;
+    int* row2col;
+    double eps;
+    int budget;
+    int pad;
+};
+
 template <typename T> struct NarrowShared
 {
+    NarrowInvariants inv;
     Top2<T> part[kWarpsPerBlock];
     int q[kNarrowMax];      // controller: bidders of the round, then the next list
+    int q2[kNarrowMax];     // cached controller: the other buffer of the bidder list
+    int prev[kNarrowMax];   // cached controller: owner of the column each bidder bid for
     int col[kNarrowMax];    // controller: column each bidder bid for
     double bid[kNarrowMax]; // controller: its bid
     int warp_count[kWarpsPerBlock];
     int head, qn, stop;
+    int round_no; // cached controller: rounds of the current call
+    long long ctr[4]; // cached controller: bids, misses, fallbacks of the call (thread 0)
+    int nmiss2[2]; // cached controller: bidders of the round whose cache could not answer (by round parity)
     double pmax;
     long long dbg[16]; // cycle counters (B200LSAP_TIMING builds)
 };
@@ -854,6 +877,11 @@ __device__ __forceinline__ void narrow_controller(const DenseState<T>& s, Narrow
 #endif
 }
 
+} // namespace b200lsap
+#include "dense_cache.cuh"
+namespace b200lsap
+{
+
 // Start of an eps phase: prices are kept, every assignment is dropped, all rows bid again.
 template <typename T>
 __device__ __forceinline__ void reset_phase(const DenseState<T>& s, int* __restrict__ list, long long tid,
@@ -872,7 +900,8 @@ __device__ __forceinline__ void reset_phase(const DenseState<T>& s, int* __restr
 // Persistent cooperative kernel: the whole solve in one launch, the host is not touched per
 // round (north_star (3)).  Launch with cudaLaunchCooperativeKernel, one CTA per SM.
 // ---------------------------------------------------------------------------------------------
-template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(DenseState<T> s)
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid_constant__ DenseState<T> s)
 {
     cg::grid_group grid = cg::this_grid();
     const int lane = threadIdx.x & 31;
@@ -882,6 +911,7 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
     const long long n_threads = (long long)gridDim.x * kThreads;
     volatile DenseCtrl* ctrl = s.ctrl;
     __shared__ NarrowShared<T> narrow_sh;
+    __shared__ BuildShared build_sh;
 
     int cur = 0;
     int phase = 0;
@@ -893,7 +923,8 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
     NarrowCounts ncnt{0, 0, 0, 0};
     double eps = ctrl->eps[0];
     const double amax = ctrl->amax;
-    const int narrow_rows = min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
+    const bool cached = sizeof(T) == 4 && s.use_cache;
+    const int narrow_rows = cached ? min(s.narrow_rows, kNarrowMax) : min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
 
     // phase 0 starts from the state the host prepared: list[0] = all rows, count[0] = rows
     for (;;)
@@ -923,11 +954,31 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_auction_p
         {
             // narrow rounds / Gauss-Seidel tail: finishes the phase without a grid sync per round
             mode_count++;
-            if (blockIdx.x == 0)
-                narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent,
-                                     ncnt);
-            else
-                narrow_scanner<T>(s, narrow_sh, seq, amax);
+            bool done = false;
+            if constexpr (sizeof(T) == 4)
+            {
+                if (cached)
+                {
+                    // a fresh cache for every row, then CTA 0 runs the rounds alone; the other CTAs
+                    // park on their mailboxes (a grid barrier would have 147 SMs poll one address)
+                    cache_build_sweep(s, build_sh, filter_margin(amax, fmax(ctrl->pmax, amax)));
+                    grid.sync();
+                    if (blockIdx.x == 0)
+                        narrow_controller_cached(s, narrow_sh, build_sh, s.list[cur], n, mode_count, eps, amax,
+                                                 max_rounds - spent, ncnt);
+                    else
+                        narrow_scanner<T>(s, narrow_sh, seq, amax);
+                    done = true;
+                }
+            }
+            if (!done)
+            {
+                if (blockIdx.x == 0)
+                    narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent,
+                                         ncnt);
+                else
+                    narrow_scanner<T>(s, narrow_sh, seq, amax);
+            }
             grid.sync();
             if (ctrl->status != 0)
                 break;
@@ -1014,6 +1065,13 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.slots[j] = BidSlot{0ull, 0ull};
     for (long long k = tid; k < (long long)s.rows * kCand; k += n_threads)
         s.cand[k] = make_int2(-1, 0);
+    if (s.cache_hdr)
+    {
+        for (long long i = tid; i < s.rows; i += n_threads)
+            s.cache_hdr[i] = RowCacheHdr{0.0, 0, 0};
+        for (long long k = tid; k < (long long)s.rows * kCacheK; k += n_threads)
+            s.cache[k] = make_int2(0, 0); // every slot always names a real column (warp_cache_eval)
+    }
     if (tid == 0)
     {
         s.ctrl->count[0] = s.rows;
@@ -1025,6 +1083,7 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.ctrl->phase = 0;
         s.ctrl->rounds = 0;
         s.ctrl->bids = 0;
+        s.ctrl->cache_hits = s.ctrl->cache_misses = s.ctrl->cache_fallbacks = 0;
         s.narrow->arrived = 0u;
     }
     if (tid < kNarrowMax)

@@ -16,6 +16,19 @@ namespace b200lsap
 constexpr int kMaxPhases = 48;
 constexpr int kCand = 32;       // candidate (column, a) pairs kept per row: slot = (column / 4) % 32
 constexpr int kNarrowMax = 256; // power of two >= the largest narrow round (SMs - 1 bidders)
+constexpr int kCacheK = 32;     // row cache: the best (column, a) pairs of a row at its last CTA scan, one per lane
+constexpr int kSurvCap = 256;   // most elements a CTA scan may pass on to the exact evaluation
+constexpr int kProbeRows = 128; // rows sampled to size the first eps of the scaling schedule
+
+// Row cache header (dense_cache.cuh): `count` valid entries in cache[row][0..count); every element of
+// the row that is NOT cached had a - p <= bound when the cache was built.  Prices never decrease,
+// so that stays true, and a bid whose second best cached value exceeds `bound` is exact.
+struct __align__(16) RowCacheHdr
+{
+    double bound;
+    int count;
+    int pad;
+};
 
 // Controller block, one per solve, in device memory (mirrored to pinned host memory at the end).
 struct DenseCtrl
@@ -32,6 +45,14 @@ struct DenseCtrl
     long long gs_bids;      // bids placed by the Gauss-Seidel tail (included in bids)
     long long gs_episodes;  // times the tail ran
     long long dbg[16];      // cycle counters of the narrow rounds / tail (B200LSAP_TIMING builds)
+    long long cache_hits;   // narrow-round bids answered from the row cache alone
+    long long cache_misses; // narrow-round bids that needed a CTA scan of the row
+    long long cache_fallbacks; // CTA scans that fell back to the unfiltered path (ties, overflow, < 2 edges)
+    int eps_auto;           // 1: k_schedule derives eps[0] from the probe (square problems, fp32)
+    int pad1;
+    double eps_factor;
+    double eps_final;
+    double probe[kProbeRows]; // best minus cache bound of the sampled rows at the initial prices, < 0: no sample
     double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)
     double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
@@ -94,6 +115,9 @@ template <typename T> struct DenseState
     int narrow_rows; // a round with at most this many bidders (and at most SMs - 1) runs as a narrow round
     int tail_rows;   // a round with at most this many bidders is finished by the Gauss-Seidel tail (0: never)
     int dry;         // 1: measurement sweep, bids are computed and stored but not offered
+    int2* cache;           // [rows][kCacheK] (column, bits of a), best first (fp32 problems only)
+    RowCacheHdr* cache_hdr; // [rows]
+    int use_cache;         // 1: narrow rounds answer from the row cache (fp32, persistent driver)
 };
 
 // ---------------------------------------------------------------------------------------------

@@ -62,7 +62,7 @@ class Handle:
 
     @staticmethod
     def _opts(eps_multiplier=None, eps_scaling=None, eps_start=None, eps_factor=None, max_rounds=None,
-              driver=None, tail_rows=None, narrow_rows=None) -> Options:
+              driver=None, tail_rows=None, narrow_rows=None, row_cache=None) -> Options:
         o = Options()
         _capi.lib().b200lsap_options_default(C.byref(o))
         if eps_multiplier is not None:
@@ -77,6 +77,8 @@ class Handle:
             o.max_rounds = max_rounds
         if driver is not None:
             o.driver = driver
+        if row_cache is not None:
+            o.row_cache = row_cache
         if tail_rows is not None:
             o.tail_rows = tail_rows
         if narrow_rows is not None:

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B200LSAP_VERSION 100
+#define B200LSAP_VERSION 101
 
 #define B200LSAP_COL_MAJOR 0 /* Eigen::Matrix default: a(i,j) = a[i + j*ld] */
 #define B200LSAP_ROW_MAJOR 1 /* a(i,j) = a[i*ld + j] */
@@ -62,7 +62,9 @@ typedef struct
 {
     double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
     int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on */
-    double eps_start;      /* first eps of the scaling schedule; <= 0: default */
+    double eps_start;      /* first eps of the scaling schedule; <= 0: default (fp32: a quarter of the mean
+                              spread of a row's best ~36 values, measured on sampled rows, at most 0.25;
+                              fp64: 0.25).  Only the LAST phase, at eps_multiplier / cols, decides the result. */
     double eps_factor;     /* eps is divided by this between phases; <= 1: default */
     int64_t max_rounds;    /* watchdog; <= 0: default */
     int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
@@ -73,7 +75,9 @@ typedef struct
     int32_t narrow_rows;   /* a round with at most this many bidders (and at most SMs - 1) runs as a
                               narrow round: one CTA per bidder row, a controller CTA instead of grid
                               syncs; 0: default (SMs - 1), -1: never.  Persistent driver only. */
-    int32_t reserved;
+    int32_t row_cache;     /* narrow rounds answer from per-row caches of the best columns instead of
+                              scanning rows (fp32, persistent driver; bit-identical bids): 0 default (on),
+                              -1 off */
 } b200lsap_options;
 
 typedef struct
@@ -90,7 +94,9 @@ typedef struct
     int64_t tail_bids; /* bids placed by the Gauss-Seidel tail (included in bids, not in rounds) */
     int64_t tail_runs; /* times the tail took over */
     int64_t narrow_rounds; /* rounds run as narrow rounds (included in rounds) */
-    int64_t reserved[1];
+    int64_t cache_hits;    /* narrow-round bids answered from the row cache alone */
+    int64_t cache_misses;  /* narrow-round bids that re-scanned their row (and rebuilt its cache) */
+    double eps_first;      /* eps of the first phase */
 } b200lsap_stats;
 
 /* device < 0: the current CUDA device.  Creates the handle's own non-blocking stream. */

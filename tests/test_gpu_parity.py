@@ -29,9 +29,18 @@ def test_golden_layouts_dtypes_and_drivers_agree(handle, oracle_lib, path):
     a = _gen(oracle_lib, g)
     base, p0 = handle.solve(a, want_prices=True)                       # row-major fp32
     assert np.array_equal(base, parity.golden_row_to_col(g))
-    for variant in (np.asfortranarray(a), a.astype(np.float64), np.asfortranarray(a.astype(np.float64))):
-        r2c, p = handle.solve(variant, want_prices=True)
+    # the fp32 path sizes its first eps from the data (k_probe); handing the same eps to the other
+    # layouts / dtypes must reproduce the prices bit for bit: the fp64 path scans rows where the
+    # fp32 path answers narrow rounds from its row caches
+    e0 = handle.last_stats["eps_first"]
+    r2c, p = handle.solve(np.asfortranarray(a), want_prices=True)
+    assert np.array_equal(r2c, base) and np.array_equal(p, p0)
+    for variant in (a.astype(np.float64), np.asfortranarray(a.astype(np.float64))):
+        r2c, p = handle.solve(variant, want_prices=True, eps_start=e0)
         assert np.array_equal(r2c, base) and np.array_equal(p, p0)
+    r2c, p = handle.solve(a, want_prices=True, row_cache=-1)            # narrow rounds by row scans
+    assert handle.last_stats["cache_hits"] == 0
+    assert np.array_equal(r2c, base) and np.array_equal(p, p0)
     # host-driven rounds run the same device code without the Gauss-Seidel tail: identical to the
     # persistent kernel with the tail switched off, price for price
     r2c_j, p_j = handle.solve(a, want_prices=True, tail_rows=-1, narrow_rows=-1)

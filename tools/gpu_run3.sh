@@ -1,0 +1,5 @@
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+timeout 900 python tools/quick_bench.py "$@" > gpurun_out/quick.log 2>&1
+tail -15 gpurun_out/pytest_gpu.log; cat gpurun_out/quick.log

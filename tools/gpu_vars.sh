@@ -1,0 +1,4 @@
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+for f in "$@"; do echo "== $f"; B200LSAP_LIB=$PWD/build_timing/$f.so timeout 300 python tools/quick_bench.py c4t 2>&1 | grep -v "full bid"; done > gpurun_out/vars.log 2>&1
+cat gpurun_out/vars.log

@@ -85,6 +85,77 @@ static void build_cache(cache_t* c, const float* row, const double* p, int cols,
     c->bound = n > K ? val[K] : -INFINITY;
 }
 
+/* policy 1 (the CTA scan of the narrow rounds): 32 column groups g = (col / 128) % 32 (the warps of a
+ * 1024-thread CTA); T = the 32nd largest of the 64 values {group best, group second best}; every element
+ * above T survives; the cache keeps the K best survivors, bound = T or the (K+1)-th survivor. */
+static long long g_survivors = 0, g_builds1 = 0, g_overflow = 0;
+static int cmp_desc(const void* a, const void* b)
+{
+    const double x = *(const double*)a, y = *(const double*)b;
+    return x < y ? 1 : (x > y ? -1 : 0);
+}
+static void build_cache_stat(cache_t* c, const float* row, const double* p, int cols, int K)
+{
+    double hi[32], lo[32], cand[64];
+    for (int g = 0; g < 32; g++)
+        hi[g] = lo[g] = -INFINITY;
+    for (int j = 0; j < cols; j++)
+    {
+        const int g = (j >> 7) & 31;
+        const double d = (double)row[j] - p[j];
+        if (d > hi[g])
+        {
+            lo[g] = hi[g];
+            hi[g] = d;
+        }
+        else if (d > lo[g])
+            lo[g] = d;
+    }
+    for (int g = 0; g < 32; g++)
+    {
+        cand[g] = hi[g];
+        cand[32 + g] = lo[g];
+    }
+    qsort(cand, 64, sizeof(double), cmp_desc);
+    const double T = cand[31];
+    static __thread double sv[65536];
+    static __thread int sc[65536];
+    int n = 0;
+    for (int j = 0; j < cols; j++)
+    {
+        const double d = (double)row[j] - p[j];
+        if (d >= T)
+        {
+            sv[n] = d;
+            sc[n] = j;
+            n++;
+        }
+    }
+    __sync_fetch_and_add(&g_survivors, n);
+    __sync_fetch_and_add(&g_builds1, 1);
+    if (n > 256)
+        __sync_fetch_and_add(&g_overflow, 1);
+    /* partial selection of the K+1 best */
+    const int keep = n < K + 1 ? n : K + 1;
+    for (int k = 0; k < keep; k++)
+    {
+        int m = k;
+        for (int q = k + 1; q < n; q++)
+            if (sv[q] > sv[m])
+                m = q;
+        const double tv = sv[k];
+        sv[k] = sv[m];
+        sv[m] = tv;
+        const int tc = sc[k];
+        sc[k] = sc[m];
+        sc[m] = tc;
+    }
+    c->n = n > K ? K : n;
+    for (int k = 0; k < c->n; k++)
+        c->col[k] = sc[k];
+    c->bound = n > K ? sv[K] : T;
+}
+
 /* returns 1 when the cache alone determines best and second best exactly */
 static int cache_answers(const cache_t* c, const float* row, const double* p)
 {
@@ -115,6 +186,10 @@ int main(int argc, char** argv)
     const int keep_assign = argc > 8 ? atoi(argv[8]) : 0;
     const int n_slots = argc > 9 ? atoi(argv[9]) : 0; /* GS mode: LRU of this many cached rows (0: unlimited) */
     const int early = argc > 10 ? atoi(argv[10]) : 0; /* non-final phases stop once <= early rows are unassigned */
+    const int narrow_T = argc > 11 ? atoi(argv[11]) : 0; /* policy 1: caches are built and used only in rounds with <= narrow_T bidders */
+    const int policy2 = argc > 12 ? atoi(argv[12]) : 0;
+    long long entry_builds = 0;
+    long long nr_rounds[4] = {0, 0, 0, 0}, nr_bids = 0, nr_miss = 0; /* narrow rounds with 0, 1, 2-4, >4 misses */
     int* slot_row = n_slots > 0 ? malloc(n_slots * sizeof(int)) : NULL;
     long long* slot_age = n_slots > 0 ? calloc(n_slots, sizeof(long long)) : NULL;
     for (int k = 0; k < n_slots; k++)
@@ -186,6 +261,7 @@ int main(int argc, char** argv)
             }
         }
         long long ph_rounds = 0, ph_bids = 0;
+        int in_narrow = 0;
         long long ph_gs = 0;
         while (n > 0)
         {
@@ -233,7 +309,10 @@ int main(int argc, char** argv)
                         }
                         else
                         {
-                            build_cache(&cache[i], A + (size_t)i * cols, p, cols, K);
+                            if (narrow_T > 0)
+                                build_cache_stat(&cache[i], A + (size_t)i * cols, p, cols, K);
+                            else
+                                build_cache(&cache[i], A + (size_t)i * cols, p, cols, K);
                             has_cache[i] = 1;
                             cache_builds++;
                             gs_miss++;
@@ -276,7 +355,42 @@ int main(int argc, char** argv)
                 const int i = list[k];
                 bid[k] = scan_row(A + (size_t)i * cols, p, cols);
             }
-            if (K > 0)
+            if (K > 0 && narrow_T > 0)
+            {
+                if (n <= narrow_T)
+                {
+                    int miss = 0;
+                    if (!in_narrow && policy2)
+                    {
+                        /* policy 2: entering the narrow regime of this phase, every row gets a fresh cache */
+#pragma omp parallel for schedule(dynamic, 16)
+                        for (int i = 0; i < rows; i++)
+                        {
+                            build_cache_stat(&cache[i], A + (size_t)i * cols, p, cols, K);
+                            has_cache[i] = 1;
+                        }
+                        entry_builds += rows;
+                    }
+                    in_narrow = 1;
+                    for (int k = 0; k < n; k++)
+                    {
+                        const int i = list[k];
+                        if (has_cache[i] && cache_answers(&cache[i], A + (size_t)i * cols, p))
+                            cache_hits++;
+                        else
+                        {
+                            build_cache_stat(&cache[i], A + (size_t)i * cols, p, cols, K);
+                            has_cache[i] = 1;
+                            cache_builds++;
+                            miss++;
+                        }
+                    }
+                    nr_rounds[miss == 0 ? 0 : miss == 1 ? 1 : miss <= 4 ? 2 : 3]++;
+                    nr_bids += n;
+                    nr_miss += miss;
+                }
+            }
+            else if (K > 0)
             {
 #pragma omp parallel for schedule(dynamic, 16) reduction(+ : cache_hits, cache_builds) if (n >= 256)
                 for (int k = 0; k < n; k++)
@@ -348,6 +462,25 @@ int main(int argc, char** argv)
         printf("GS-mode cache (slots %d): hits %lld misses %lld\n", n_slots, gs_hits, gs_miss);
     if (K > 0)
         printf("cache: hits %lld, builds (full scans) %lld\n", cache_hits, cache_builds);
+    {
+        /* cost model (us): wide round 16 + bandwidth at 5 TB/s, narrow round 1.5 + 2.5 per miss, tail bid 1.2 + 2.5 per miss,
+         * cache build sweep per phase = one matrix read at 2.5 TB/s */
+        const long long narrow_r = nr_rounds[0] + nr_rounds[1] + nr_rounds[2] + nr_rounds[3];
+        const long long wide_r = rounds - narrow_r;
+        const long long wide_b = bids - gs_bids - nr_bids;
+        const double row_us = cols * 4.0 / 5.0e6;
+        const double cost = 16.0 * wide_r + row_us * wide_b + 1.5 * narrow_r + 2.5 * (nr_miss + gs_miss) + 1.2 * gs_bids +
+                            (policy2 ? entry_builds * row_us * 2.0 : 0.0);
+        printf("COST %.1f ms: phases %d wide rounds %lld (bids %lld) narrow rounds %lld (misses %lld) tail bids %lld (misses %lld)\n",
+               cost / 1e3, nph, wide_r, wide_b, narrow_r, nr_miss, gs_bids, gs_miss);
+    }
+    if (policy2)
+        printf("policy 2: %lld cache builds at narrow-regime entries\n", entry_builds);
+    if (narrow_T > 0)
+        printf("policy 1 (narrow <= %d): narrow rounds with 0 / 1 / 2-4 / >4 misses: %lld / %lld / %lld / %lld; bids %lld misses %lld; "
+               "survivors per build %.1f, builds %lld, >256 survivors %lld\n",
+               narrow_T, nr_rounds[0], nr_rounds[1], nr_rounds[2], nr_rounds[3], nr_bids, nr_miss,
+               g_builds1 ? (double)g_survivors / g_builds1 : 0.0, g_builds1, g_overflow);
     printf("bidders/round histogram (jacobi rounds only):\n");
     for (int b = 0; b < 40; b++)
         if (hist_r[b])

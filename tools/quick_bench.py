@@ -15,7 +15,8 @@ def dense(rows, cols, seed=1, reps=3, **opt):
         if best is None or st["ms_solve"] < best["ms_solve"]: best = st
     gbs = best["bid_bytes"] / best["ms_solve"] / 1e6
     print(f"dense {rows}x{cols} {opt}: {best['ms_solve']:.3f} ms rounds {best['rounds']} bids {best['bids']} phases {best['phases']} narrow {best['narrow_rounds']} tail {best['tail_bids']}/{best['tail_runs']} "
-          f"us/round {1e3*best['ms_solve']/max(best['rounds'],1):.2f} alg GB/s {gbs:.0f}", flush=True)
+          f"us/round {1e3*best['ms_solve']/max(best['rounds'],1):.2f} alg GB/s {gbs:.0f} "
+          f"cache hit/miss {best['cache_hits']}/{best['cache_misses']} eps0 {best['eps_first']:.3g}", flush=True)
     dbg = h.debug_counters()
     if any(dbg):
         print("   dbg cycles:", dbg, flush=True)
@@ -48,10 +49,16 @@ if __name__ == "__main__":
             print(f"sweep 16384^2: {ms:.4f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
-    if "c4d" in which:
-        dense(16384, 16384, reps=1)
-        dense(16384, 16384, reps=1, tail_rows=-1)
-        dense(16384, 16384, reps=1, tail_rows=1)
+    if "c4t" in which:
+        dense(16384, 16384, reps=2)
+    if "c4n" in which:
+        dense(16384, 16384, reps=2)
+        dense(16384, 16384, reps=1, eps_start=0.25)
+        dense(16384, 16384, reps=1, row_cache=-1)
+        dense(16384, 16384, reps=1, row_cache=-1, eps_start=0.25)
+        dense(16384, 16384, reps=1, seed=2)
+        dense(16384, 16384, reps=1, seed=3)
+        dense(8192, 8192, reps=1)
     if "c4" in which:
         for opt in (dict(), dict(tail_rows=1), dict(tail_rows=4), dict(tail_rows=8), dict(narrow_rows=-1, tail_rows=8),
                     dict(narrow_rows=-1, tail_rows=-1)):

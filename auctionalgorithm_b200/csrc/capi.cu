@@ -64,6 +64,7 @@ struct b200lsap_handle
     int min_seg = 512;
     int max_parts = 4;
     int64_t launches = 0;
+    double eps_probe_scale = 0.125; // developer knob B200LSAP_EPS_SCALE
     // column-sharded solve in progress (b200lsap_shard_*)
     struct
     {
@@ -180,6 +181,12 @@ int b200lsap_create(b200lsap_handle** out, int device)
         if (v >= 1 && v <= 64)
             h->max_parts = v;
     }
+    if (const char* s = getenv("B200LSAP_EPS_SCALE"))
+    {
+        const double v = atof(s);
+        if (v > 0)
+            h->eps_probe_scale = v;
+    }
     if (const char* s = getenv("B200LSAP_MIN_SEG"))
     {
         int v = atoi(s);
@@ -286,7 +293,7 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
                     "asymmetric problems (SURVEY.md section 7.3)");
     plan.eps.clear();
     plan.eps_auto = scaling && !(o.eps_start > 0);
-    plan.eps_factor = o.eps_factor > 1 ? o.eps_factor : 5.0;
+    plan.eps_factor = o.eps_factor > 1 ? o.eps_factor : 7.0;
     plan.use_cache = o.row_cache >= 0;
     if (scaling)
     {
@@ -407,6 +414,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->eps_auto = eps_auto ? 1 : 0;
     hc->eps_factor = plan.eps_factor;
     hc->eps_final = plan.eps.back();
+    hc->eps_probe_scale = h->eps_probe_scale;
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
     s.use_cache = (sizeof(T) == 4 && plan.driver == 0 && plan.use_cache) ? 1 : 0;
     std::vector<double> eps = plan.eps;
@@ -436,9 +444,46 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     if (plan.driver == 0)
     {
         void* args[] = {&s};
-        CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads), args, 0,
-                                       h->stream));
-        h->launches++;
+        if (s.use_cache)
+        {
+            // fp32 with row caches: per eps phase one cooperative launch (wide rounds, then a fresh cache
+            // for every row) and one k_narrow launch (the narrow rounds on one SM, narrow_kernel.cuh),
+            // all enqueued now; launches that find nothing left to do return at once.
+            if constexpr (sizeof(T) == 4)
+            {
+                int n_phases = (int)eps.size();
+                if (eps_auto)
+                {
+                    CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
+                    CU(cudaStreamSynchronize(h->stream));
+                    n_phases = hc->n_phases;
+                }
+                const size_t dyn = (size_t)round_up(plan.cols, 2) * sizeof(double) + (size_t)plan.cols * sizeof(int);
+                cudaFuncAttributes fa;
+                CU(cudaFuncGetAttributes(&fa, k_narrow<true>));
+                int optin = 0;
+                CU(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+                const bool smem_prices = dyn + fa.sharedSizeBytes + 1024 <= (size_t)optin;
+                if (smem_prices)
+                    CU(cudaFuncSetAttribute(k_narrow<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+                for (int p = 0; p < n_phases; p++)
+                {
+                    CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads), args,
+                                                   0, h->stream));
+                    if (smem_prices)
+                        k_narrow<true><<<1, kNarrowThreads, dyn, h->stream>>>(s);
+                    else
+                        k_narrow<false><<<1, kNarrowThreads, 0, h->stream>>>(s);
+                    h->launches += 2;
+                }
+            }
+        }
+        else
+        {
+            CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads), args, 0,
+                                           h->stream));
+            h->launches++;
+        }
         CU(cudaEventRecord(h->ev[2], h->stream));
         CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));

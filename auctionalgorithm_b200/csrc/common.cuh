@@ -188,6 +188,19 @@ __device__ __forceinline__ float4 ld_stream4(const float* p)
     return r;
 }
 
+// Same, but the line is also first in line for eviction from L2: the cache-building sweep reads the
+// whole matrix once and must not push the row caches it is writing (4 MB) out of the 126 MB L2.
+__device__ __forceinline__ float4 ld_stream4_evict_first(const float* p)
+{
+    float4 r;
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p), "l"(pol));
+    return r;
+}
+
 struct double4_t
 {
     double x, y, z, w;

@@ -482,37 +482,14 @@ __device__ __forceinline__ void prefetch_row_l2(const void* row, unsigned bytes)
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(row), "r"(bytes) : "memory");
 }
 
-// Loop invariants of the cached controller, kept in shared memory and re-read where they are used:
-// at 64 registers per thread anything held across the round loop is spilled to the stack, and a
-// stack line that takes one spill store per round costs an L2 round trip at every reload.
-struct NarrowInvariants
-{
-    const int2* cache;
-    const RowCacheHdr* hdr;
-    double* prices;
-    float* pricesf;
-    double* profits;
-    int* owner;
-    int* row2col;
-    double eps;
-    int budget;
-    int pad;
-};
-
 template <typename T> struct NarrowShared
 {
-    NarrowInvariants inv;
     Top2<T> part[kWarpsPerBlock];
     int q[kNarrowMax];      // controller: bidders of the round, then the next list
-    int q2[kNarrowMax];     // cached controller: the other buffer of the bidder list
-    int prev[kNarrowMax];   // cached controller: owner of the column each bidder bid for
     int col[kNarrowMax];    // controller: column each bidder bid for
     double bid[kNarrowMax]; // controller: its bid
     int warp_count[kWarpsPerBlock];
     int head, qn, stop;
-    int round_no; // cached controller: rounds of the current call
-    long long ctr[4]; // cached controller: bids, misses, fallbacks of the call (thread 0)
-    int nmiss2[2]; // cached controller: bidders of the round whose cache could not answer (by round parity)
     double pmax;
     long long dbg[16]; // cycle counters (B200LSAP_TIMING builds)
 };
@@ -879,6 +856,7 @@ __device__ __forceinline__ void narrow_controller(const DenseState<T>& s, Narrow
 
 } // namespace b200lsap
 #include "dense_cache.cuh"
+#include "narrow_kernel.cuh"
 namespace b200lsap
 {
 
@@ -913,18 +891,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     __shared__ NarrowShared<T> narrow_sh;
     __shared__ BuildShared build_sh;
 
-    int cur = 0;
-    int phase = 0;
+    // The fp32 solve runs as one launch per eps phase (k_narrow finishes each phase's narrow rounds in
+    // between, narrow_kernel.cuh): the loop state lives in the controller block across launches.
+    if (ctrl->done || ctrl->status != 0)
+        return;
+    int cur = ctrl->cur;
+    int phase = ctrl->phase;
     int seq = 0;        // CTA 0: sequence number of the last narrow round; scanners: last mailbox flag consumed
     int mode_count = 0; // times the grid has entered narrow mode
     const int n_phases = ctrl->n_phases;
-    const long long max_rounds = ctrl->max_rounds;
+    const long long max_rounds = ctrl->max_rounds - ctrl->rounds;
     long long rounds = 0, bids = 0;
     NarrowCounts ncnt{0, 0, 0, 0};
-    double eps = ctrl->eps[0];
+    double eps = ctrl->eps[phase];
     const double amax = ctrl->amax;
     const bool cached = sizeof(T) == 4 && s.use_cache;
     const int narrow_rows = cached ? min(s.narrow_rows, kNarrowMax) : min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
+    bool handed_over = false;
 
     // phase 0 starts from the state the host prepared: list[0] = all rows, count[0] = rows
     for (;;)
@@ -954,31 +937,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
         {
             // narrow rounds / Gauss-Seidel tail: finishes the phase without a grid sync per round
             mode_count++;
-            bool done = false;
             if constexpr (sizeof(T) == 4)
             {
-                if (cached)
+                if (cached && n <= narrow_rows)
                 {
-                    // a fresh cache for every row, then CTA 0 runs the rounds alone; the other CTAs
-                    // park on their mailboxes (a grid barrier would have 147 SMs poll one address)
+                    // a fresh cache for every row, then this launch ends: k_narrow (one SM, prices in
+                    // shared memory) finishes the phase, the next launch starts the next one
                     cache_build_sweep(s, build_sh, filter_margin(amax, fmax(ctrl->pmax, amax)));
-                    grid.sync();
-                    if (blockIdx.x == 0)
-                        narrow_controller_cached(s, narrow_sh, build_sh, s.list[cur], n, mode_count, eps, amax,
-                                                 max_rounds - spent, ncnt);
-                    else
-                        narrow_scanner<T>(s, narrow_sh, seq, amax);
-                    done = true;
+                    handed_over = true;
+                    break;
                 }
             }
-            if (!done)
-            {
-                if (blockIdx.x == 0)
-                    narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent,
-                                         ncnt);
-                else
-                    narrow_scanner<T>(s, narrow_sh, seq, amax);
-            }
+            if (blockIdx.x == 0)
+                narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent, ncnt);
+            else
+                narrow_scanner<T>(s, narrow_sh, seq, amax);
             grid.sync();
             if (ctrl->status != 0)
                 break;
@@ -1003,12 +976,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     }
     if (tid == 0)
     {
-        ctrl->rounds = rounds + ncnt.rounds;
-        ctrl->bids = bids + ncnt.bids + ncnt.gs_bids;
-        ctrl->narrow_rounds = ncnt.rounds;
-        ctrl->gs_bids = ncnt.gs_bids;
-        ctrl->gs_episodes = ncnt.gs_runs;
+        ctrl->rounds += rounds + ncnt.rounds;
+        ctrl->bids += bids + ncnt.bids + ncnt.gs_bids;
+        ctrl->narrow_rounds += ncnt.rounds;
+        ctrl->gs_bids += ncnt.gs_bids;
+        ctrl->gs_episodes += ncnt.gs_runs;
         ctrl->phase = phase;
+        ctrl->cur = cur;
+        if (!handed_over)
+            ctrl->done = 1;
     }
 }
 
@@ -1084,6 +1060,9 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.ctrl->rounds = 0;
         s.ctrl->bids = 0;
         s.ctrl->cache_hits = s.ctrl->cache_misses = s.ctrl->cache_fallbacks = 0;
+        s.ctrl->narrow_rounds = s.ctrl->gs_bids = s.ctrl->gs_episodes = 0;
+        s.ctrl->cur = 0;
+        s.ctrl->done = 0;
         s.narrow->arrived = 0u;
     }
     if (tid < kNarrowMax)

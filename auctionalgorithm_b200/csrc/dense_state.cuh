@@ -49,9 +49,12 @@ struct DenseCtrl
     long long cache_misses; // narrow-round bids that needed a CTA scan of the row
     long long cache_fallbacks; // CTA scans that fell back to the unfiltered path (ties, overflow, < 2 edges)
     int eps_auto;           // 1: k_schedule derives eps[0] from the probe (square problems, fp32)
+    int cur;                // which of list[0] / list[1] holds the bidders (kept across the launches of a solve)
+    int done;               // the last phase has finished
     int pad1;
     double eps_factor;
     double eps_final;
+    double eps_probe_scale; // eps[0] = this fraction of the mean probe spread (default 1/4)
     double probe[kProbeRows]; // best minus cache bound of the sampled rows at the initial prices, < 0: no sample
     double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)

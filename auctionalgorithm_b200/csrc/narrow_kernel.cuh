@@ -1,0 +1,601 @@
+// narrow_kernel.cuh — k_narrow: the narrow rounds of an eps phase on ONE SM (fp32 problems).
+//
+// Included by dense_kernels.cuh after dense_cache.cuh.
+//
+// Once a phase is down to <= kNarrowMax bidders the cooperative kernel stops (after giving every row
+// a fresh cache, dense_cache.cuh) and this single-CTA kernel finishes the phase; the host has both
+// launches of every phase enqueued beforehand and is not touched per round.  Why a kernel of its own:
+//   * a round is a chain of dependent latencies, not bandwidth.  Measured on B200 (tools/micro):
+//     L1 hit 39 cycles, L2 hit ~290, a load of a line this SM has just stored to ~660 (stores
+//     invalidate the L1 line and the load queues behind the store), shared memory ~35, bar.sync
+//     ~50-80.  Prices and owners change every round, so inside the cooperative kernel each round
+//     paid two or three L2 round trips for them;
+//   * here prices[] and owner[] live in SHARED MEMORY for the whole phase (12 bytes per column:
+//     16384 columns = 192 KB of the SM's 227 KB; global memory is written through and never read
+//     back), which the cooperative kernel cannot afford: its sweeps need that space as L1;
+//   * 512 threads at up to 128 registers instead of 1024 at 64: the round loop holds its state in
+//     registers (at 64 every loop-carried value was spilled, and a spill store per round turns the
+//     reloads from that stack line into L2 round trips);
+//   * the top-2 of the 32 cached values is five redux.sync on the ordered bits of the doubles
+//     instead of five levels of 64-bit shuffles and dependent fp64 compares (~200 vs ~550 cycles);
+//   * a round with ONE bidder (most rounds of a square problem) never leaves warp 0: evaluate, bid,
+//     evict, continue with the evicted row, no barrier and no shared-memory exchange.
+// The rounds themselves are unchanged (Jacobi rounds of the n unassigned rows; highest bid per
+// column, lowest row among equal bids; price / lock / evict as Auction.h:250-285), so prices come out
+// bit-identical to the row-scanning paths (tests: test_golden_layouts_dtypes_and_drivers_agree).
+#pragma once
+
+namespace b200lsap
+{
+
+constexpr int kNarrowThreads = 512;
+constexpr int kNarrowWarps = kNarrowThreads / 32;
+constexpr int kMissMark = -2;
+
+struct NarrowKShared
+{
+    BuildShared bs;
+    Top2<float> part[kNarrowWarps]; // unfiltered fallback scan
+    int q[2][kNarrowMax];           // bidders of the round / of the next round
+    int col[kNarrowMax];            // column each bidder bid for (kMissMark: cache could not answer)
+    int prev[kNarrowMax];           // current owner of that column
+    double bid[kNarrowMax];
+    int warp_count[kNarrowWarps];
+    int qn, stop, nmiss, served;
+    double pmax;
+    Top2<float> res; // result of the fallback scan
+};
+
+// Order-preserving map of a double to u64 (larger double <=> larger key); -0.0 is folded into +0.0
+// first so that equal values have equal keys, as the reference's '>' sees them.
+__device__ __forceinline__ unsigned long long ordered_key(double v)
+{
+    const long long b = __double_as_longlong(v + 0.0);
+    return (unsigned long long)(b ^ ((b >> 63) | (long long)0x8000000000000000ull));
+}
+__device__ __forceinline__ double key_to_double(unsigned long long k)
+{
+    const long long b = (long long)k;
+    return __longlong_as_double(b < 0 ? (b ^ (long long)0x8000000000000000ull) : ~b);
+}
+
+// One warp: best / second best of row i from its cache (dense_cache.cuh) and the current prices.
+// Returns true (all lanes) when the answer is exact; t then holds it in every lane and `prev` the
+// current owner of the best column.  Unused cache slots hold a == 0 ("no edge", Auction.h:134).
+// Tie rules: the best is the largest value, lowest column among equals (strict '>' in column
+// order, Auction.h:136); the second best may equal the best (Auction.h:147-148).
+#ifdef B200LSAP_TIMING
+__device__ long long g_ev[8]; // developer counters of the one-bidder path
+#endif
+
+template <bool kSmem, bool kChase = false>
+__device__ __forceinline__ bool narrow_eval(const DenseState<float>& s, const double* prices_s, const int* owner_s,
+                                            int i, int lane, Top2<float>& t, int& prev, long long* evp = nullptr)
+{
+#ifdef B200LSAP_TIMING
+    long long ev0 = clock64();
+#define EVTICK(k, ...)                                                                                             \
+    do                                                                                                             \
+    {                                                                                                              \
+        if (kChase)                                                                                                \
+        {                                                                                                          \
+            asm volatile("" ::__VA_ARGS__ : "memory");                                                             \
+            const long long now_ = clock64();                                                                      \
+            evp[k] += now_ - ev0;                                                                                  \
+            ev0 = now_;                                                                                            \
+        }                                                                                                          \
+    } while (0)
+#else
+#define EVTICK(k, ...)
+#endif
+    const int2 e = s.cache[(long long)i * kCacheK + lane];
+    const RowCacheHdr h = s.cache_hdr[i];
+    EVTICK(0, "r"(e.x), "r"(e.y), "r"(h.count));
+    const float a = __int_as_float(e.y);
+    double p;
+    int own;
+    if (kSmem)
+    {
+        p = prices_s[e.x];
+        own = owner_s[e.x];
+    }
+    else
+    {
+        p = __ldcg(s.prices + e.x);
+        own = __ldcg(s.owner + e.x);
+    }
+    EVTICK(1, "d"(p), "r"(own));
+    const bool valid = a != 0.f && lane < h.count;
+    if (kChase && lane < 4 && valid && own >= 0)
+    {
+        // one-bidder chain: the next bidder is the owner of the column this row takes, most likely one
+        // of the row's best few columns; pull those owners' caches towards L1 while the top-2 is reduced
+        prefetch_l1(s.cache + (long long)own * kCacheK);
+        prefetch_l1(s.cache + (long long)own * kCacheK + kCacheK / 2);
+        prefetch_l1(s.cache_hdr + own);
+    }
+    const unsigned long long key = valid ? ordered_key(widen_exact(a) - p) : 0ull;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    // best: max of the high words, then of the low words among those, then the lowest column
+    const unsigned mh = __reduce_max_sync(kFullMask, hi);
+    const bool c1 = valid && hi == mh;
+    const unsigned ml = __reduce_max_sync(kFullMask, c1 ? lo : 0u);
+    const bool top = c1 && lo == ml;
+    const int mj = (int)__reduce_min_sync(kFullMask, top ? (unsigned)e.x : 0xffffffffu);
+    const bool winner = top && e.x == mj;
+    // second best: the same without the winner
+    const unsigned hi2 = winner ? 0u : hi;
+    const unsigned mh2 = __reduce_max_sync(kFullMask, hi2);
+    const unsigned ml2 = __reduce_max_sync(kFullMask, (!winner && valid && hi == mh2) ? lo : 0u);
+    EVTICK(2, "r"(mh2), "r"(ml2), "r"(mj));
+    const unsigned wmask = __ballot_sync(kFullMask, winner);
+    const int src = wmask ? __ffs(wmask) - 1 : 0;
+    t.a = __shfl_sync(kFullMask, a, src);
+    prev = __shfl_sync(kFullMask, own, src);
+    t.j = wmask ? mj : -1;
+    t.v = key_to_double(((unsigned long long)mh << 32) | ml);
+    const unsigned long long k2 = ((unsigned long long)mh2 << 32) | ml2;
+    t.w = k2 ? key_to_double(k2) : -kNoSecondBest;
+    EVTICK(3, "r"(prev), "f"(t.a), "d"(t.w));
+    // w above the -1e6 start value of the scan (Auction.h:237) and above `bound` beats every
+    // column outside the cache
+    return h.count >= 2 && wmask != 0 && k2 != 0 && t.w > h.bound && t.w > -kNoSecondBest;
+}
+
+// Every thread: unfiltered scan of row i (ties, too few edges), with the -1e6 rescue of rescue_scan.
+// Result in sh.res, valid after the trailing barrier.
+__device__ __noinline__ void narrow_exact_scan(const DenseState<float>& s, NarrowKShared& sh, int i)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* __restrict__ row = s.A + (long long)i * s.ld;
+    Top2<float> t = top2_empty<float>();
+    for (int c = tid * 4; c < s.cols4; c += 4 * kNarrowThreads)
+    {
+        const float4 a = ld_stream4(row + c);
+        top2_push(t, a.x, s.prices[c], c);
+        top2_push(t, a.y, s.prices[c + 1], c + 1);
+        top2_push(t, a.z, s.prices[c + 2], c + 2);
+        top2_push(t, a.w, s.prices[c + 3], c + 3);
+    }
+    top2_warp_reduce(t);
+    if (lane == 0)
+        sh.part[warp] = t;
+    __syncthreads();
+    if (warp == 0)
+    {
+        Top2<float> m = lane < kNarrowWarps ? sh.part[lane] : top2_empty<float>();
+        top2_warp_reduce(m);
+        m = rescue_scan(s, i, m, lane);
+        if (lane == 0)
+            sh.res = m;
+    }
+    __syncthreads();
+}
+
+// Every thread: bidders whose cache could not answer get a CTA scan (which rebuilds the cache).
+template <bool kSmem>
+__device__ __noinline__ void narrow_misses(const DenseState<float>& s, NarrowKShared& sh, const int* owner_s, const int* q,
+                                           int n, double eps, double amax)
+{
+    const int tid = threadIdx.x;
+    const float margin = filter_margin(amax, sh.pmax);
+    for (int b = 0; b < n; b++)
+    {
+        if (sh.col[b] != kMissMark) // the same for every thread
+            continue;
+        const int i = q[b];
+        int j = -1;
+        float a = 0.f;
+        double w = 0.0;
+        if (cta_scan_build<kNarrowThreads>(s, sh.bs, i, margin))
+        {
+            j = sh.bs.j;
+            a = sh.bs.a;
+            w = sh.bs.w;
+        }
+        else
+        {
+            if (tid == 0)
+                s.ctrl->cache_fallbacks++;
+            __syncthreads();
+            narrow_exact_scan(s, sh, i);
+            j = sh.res.j;
+            a = sh.res.a;
+            w = sh.res.w;
+        }
+        if (tid == 0)
+        {
+            if (j < 0)
+            {
+                s.ctrl->status = 2; // B200LSAP_ERR_INFEASIBLE: the reference would never return
+                sh.stop = 1;
+                sh.col[b] = -1;
+            }
+            else
+            {
+                sh.col[b] = j;
+                sh.prev[b] = kSmem ? owner_s[j] : s.owner[j];
+                sh.bid[b] = (double)a - w + eps; // Auction.h:250
+                s.profits[i] = w - eps;          // Auction.h:253
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// price / lock / evict of one winning bid (Auction.h:259-270), shared-memory mirror first
+template <bool kSmem>
+__device__ __forceinline__ void narrow_commit(const DenseState<float>& s, double* prices_s, int* owner_s, int row, int col,
+                                              double bid, int prev)
+{
+    if (kSmem)
+    {
+        prices_s[col] = bid;
+        owner_s[col] = row;
+    }
+    s.prices[col] = bid;
+    s.pricesf[col] = (float)bid;
+    s.owner[col] = row;
+    s.row2col[row] = col;
+    if (prev >= 0)
+        s.row2col[prev] = -1;
+}
+
+template <bool kSmem>
+__global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_constant__ DenseState<float> s)
+{
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    __shared__ NarrowKShared sh;
+    double* const prices_s = reinterpret_cast<double*>(dyn_smem);
+    int* const owner_s = reinterpret_cast<int*>(prices_s + ((s.cols + 1) & ~1));
+    DenseCtrl* const ctrl = s.ctrl;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (ctrl->done || ctrl->status != 0)
+        return;
+    const int cur = ctrl->cur;
+    int n = ctrl->count[cur];
+    if (n <= 0 || n > kNarrowMax)
+        return;
+    const double eps = ctrl->eps[ctrl->phase];
+    const double amax = ctrl->amax;
+    const long long budget_ll = ctrl->max_rounds - ctrl->rounds;
+    const int budget = (int)max(0ll, min(budget_ll, 0x7fffffffll));
+#ifdef B200LSAP_TIMING
+    const long long t_begin = clock64();
+#endif
+    if (kSmem)
+        for (int j = tid; j < s.cols; j += kNarrowThreads)
+        {
+            prices_s[j] = s.prices[j];
+            owner_s[j] = s.owner[j];
+        }
+#if B200LSAP_VAR == 3
+    {
+        // experiment: pull every row cache into L2
+        int acc = 0;
+        const int4* c4 = reinterpret_cast<const int4*>(s.cache);
+        const long long n4 = (long long)s.rows * kCacheK / 2;
+        for (long long k = tid; k < n4; k += kNarrowThreads)
+            acc += __ldcg(c4 + k).x;
+        const int4* h4 = reinterpret_cast<const int4*>(s.cache_hdr);
+        for (long long k = tid; k < s.rows; k += kNarrowThreads)
+            acc += __ldcg(h4 + k).z;
+        if (acc == 0x7fffffff)
+            sh.stop = 1;
+    }
+#endif
+    // bidders in increasing row order (rank sort), so that the outcome does not depend on the order
+    // in which the wide rounds' atomics compacted the list
+    const int* __restrict__ list = s.list[cur];
+    if (tid < n)
+    {
+        const int mine = list[tid];
+        int rank = 0;
+        for (int k = 0; k < n; k++)
+            rank += list[k] < mine;
+        sh.q[0][rank] = mine;
+    }
+    if (tid == 0)
+    {
+        sh.qn = n;
+        sh.stop = 0;
+        sh.nmiss = 0;
+        sh.served = 0;
+        sh.pmax = fmax(ctrl->pmax, amax);
+    }
+    __syncthreads();
+    int rounds = 0, buf = 0;
+    long long bids = 0, misses = 0, fast = 0;
+#ifdef B200LSAP_TIMING
+    long long acc2 = 0, acc3 = 0, acc4 = 0, acc5 = 0, acc6 = 0, acc7 = 0;
+    long long bk_c0 = 0, bk_c1 = 0, bk_c2 = 0, bk_c3 = 0, bk_r0 = 0, bk_r1 = 0, bk_r2 = 0, bk_r3 = 0;
+#endif
+    for (;;)
+    {
+        n = sh.qn;
+        if (n == 0 || sh.stop)
+            break;
+        if (rounds >= budget)
+        {
+            if (tid == 0)
+                ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS
+            break;
+        }
+        int* const q = sh.q[buf];
+        int* const qn = sh.q[buf ^ 1];
+#ifdef B200LSAP_TIMING
+        long long tk = clock64();
+#define NTICK(k)                                                                                                   \
+    do                                                                                                             \
+    {                                                                                                              \
+        if (tid == 0)                                                                                              \
+        {                                                                                                          \
+            const long long now_ = clock64();                                                                      \
+            acc##k += now_ - tk;                                                                                   \
+            tk = now_;                                                                                             \
+        }                                                                                                          \
+    } while (0)
+#else
+#define NTICK(k)
+#endif
+        if (n == 1)
+        {
+            // ---- one bidder: warp 0 alone, bid after bid along the eviction chain ------------------
+            if (warp == 0)
+            {
+                int i = q[0], served = 0, left = 1;
+#ifdef B200LSAP_TIMING
+                long long evr[4] = {0, 0, 0, 0};
+                long long* const evq = evr;
+#else
+                long long* const evq = nullptr;
+#endif
+                for (;;)
+                {
+                    Top2<float> t;
+                    int prev;
+                    if (!narrow_eval<kSmem, true>(s, prices_s, owner_s, i, lane, t, prev, evq))
+                        break; // the general round below scans the row
+                    if (lane == 0)
+                    {
+                        const double bid = (double)t.a - t.w + eps; // Auction.h:250
+                        s.profits[i] = t.w - eps;                   // Auction.h:253
+                        narrow_commit<kSmem>(s, prices_s, owner_s, i, t.j, bid, prev);
+                        if (bid > sh.pmax)
+                            sh.pmax = bid;
+                    }
+                    served++;
+                    if (prev < 0)
+                    {
+                        left = 0;
+                        break;
+                    }
+                    i = prev;
+                    if (rounds + served >= budget)
+                        break;
+                    __syncwarp(); // lane 0's shared-memory prices before the next gather
+                }
+                if (lane == 0)
+                {
+                    q[0] = i;
+                    sh.qn = left;
+                    sh.served = served;
+#ifdef B200LSAP_TIMING
+                    for (int k = 0; k < 4; k++)
+                        g_ev[k] += evr[k];
+#endif
+                }
+            }
+            NTICK(2);
+            __syncthreads();
+            const int served = sh.served;
+            rounds += served;
+            bids += served;
+            fast += served;
+            n = sh.qn;
+            if (n == 0 || rounds >= budget)
+            {
+                __syncthreads(); // sh.served is rewritten by the next fast episode
+                continue;
+            }
+            // a miss: fall through, the bidder q[0] takes the general round
+        }
+#ifdef B200LSAP_TIMING
+        const long long t_round = clock64();
+#endif
+        // ---- bids from the caches: a warp per bidder -------------------------------------------------
+        for (int b = warp; b < n; b += kNarrowWarps)
+        {
+            const int i = q[b];
+            Top2<float> t;
+            int prev;
+            const bool hit = narrow_eval<kSmem>(s, prices_s, owner_s, i, lane, t, prev);
+            if (lane == 0)
+            {
+                if (hit)
+                {
+                    sh.col[b] = t.j;
+                    sh.prev[b] = prev;
+                    sh.bid[b] = (double)t.a - t.w + eps; // Auction.h:250
+                    s.profits[i] = t.w - eps;            // Auction.h:253
+                }
+                else
+                {
+                    sh.col[b] = kMissMark;
+                    atomicAdd(&sh.nmiss, 1);
+                }
+            }
+        }
+        NTICK(3);
+        __syncthreads();
+        NTICK(4);
+        const int nmiss = sh.nmiss;
+        if (nmiss > 0)
+        {
+            narrow_misses<kSmem>(s, sh, owner_s, q, n, eps, amax); // ends with a barrier
+            if (tid == 0)
+                sh.nmiss = 0;
+            if (sh.stop)
+                break;
+            misses += nmiss;
+        }
+        // ---- resolve: highest bid per column, lowest row among equal bids ------------------------------
+        if (n <= 32)
+        {
+            // one warp, in registers: match.any groups the bidders by column; only contested columns
+            // (rare) cost a reduction each
+            if (warp == 0)
+            {
+                const bool act = lane < n;
+                const int my_row = act ? q[lane] : -1;
+                const int my_col = act ? sh.col[lane] : -1 - lane;
+                const double my_bid = act ? sh.bid[lane] : 0.0;
+                int my_prev = act ? sh.prev[lane] : -1;
+                // columns first (match.any costs ~11 cycles per distinct value on sm_100: 370 for 32
+                // distinct columns); only a round with a contested column compares bids
+                bool dup = false;
+                for (int k = 0; k < n; k++)
+                {
+                    const int oc = __shfl_sync(kFullMask, my_col, k);
+                    dup |= oc == my_col && k != lane;
+                }
+                bool win = act;
+                if (__any_sync(kFullMask, dup))
+                    for (int k = 0; k < n; k++)
+                    {
+                        const int oc = __shfl_sync(kFullMask, my_col, k);
+                        const double ob = __shfl_sync(kFullMask, my_bid, k);
+                        const int orow = __shfl_sync(kFullMask, my_row, k);
+                        if (k != lane && oc == my_col && (ob > my_bid || (ob == my_bid && orow < my_row)))
+                            win = false;
+                    }
+                NTICK(7);
+                if (win)
+                {
+                    if (my_prev >= 0)
+                    {
+                        // the evicted row bids next round: start pulling its cache towards this SM
+                        prefetch_l1(s.cache + (long long)my_prev * kCacheK);
+                        prefetch_l1(s.cache + (long long)my_prev * kCacheK + kCacheK / 2);
+                        prefetch_l1(s.cache_hdr + my_prev);
+                    }
+                    narrow_commit<kSmem>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
+                    if (my_bid > sh.pmax)
+                        atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),
+                                  (unsigned long long)__double_as_longlong(my_bid));
+                }
+                // next list, in bidder order: a loser stays, a winner hands its place to the row it evicted
+                const int push = act ? (win ? my_prev : my_row) : -1;
+                const unsigned mask = __ballot_sync(kFullMask, push >= 0);
+                if (push >= 0)
+                    qn[__popc(mask & ((1u << lane) - 1))] = push;
+                if (lane == 0)
+                    sh.qn = __popc(mask);
+            }
+        }
+        else
+        {
+            int my_row = -1, my_col = -1, my_prev = -1;
+            double my_bid = 0.0;
+            bool win = false;
+            if (tid < n)
+            {
+                my_row = q[tid];
+                my_col = sh.col[tid];
+                my_bid = sh.bid[tid];
+                win = true;
+                for (int k = 0; k < n; k++)
+                    if (k != tid && sh.col[k] == my_col)
+                    {
+                        const double ob = sh.bid[k];
+                        const int orow = q[k];
+                        if (ob > my_bid || (ob == my_bid && orow < my_row))
+                            win = false;
+                    }
+                if (win)
+                {
+                    my_prev = sh.prev[tid];
+                    if (my_prev >= 0)
+                    {
+                        prefetch_l1(s.cache + (long long)my_prev * kCacheK);
+                        prefetch_l1(s.cache + (long long)my_prev * kCacheK + kCacheK / 2);
+                        prefetch_l1(s.cache_hdr + my_prev);
+                    }
+                    narrow_commit<kSmem>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
+                    if (my_bid > sh.pmax)
+                        atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),
+                                  (unsigned long long)__double_as_longlong(my_bid));
+                }
+            }
+            const int push = tid < n ? (win ? my_prev : my_row) : -1;
+            const unsigned mask = __ballot_sync(kFullMask, push >= 0);
+            if (lane == 0)
+                sh.warp_count[warp] = __popc(mask);
+            __syncthreads(); // warp_count is complete
+            int base = 0, total = 0;
+            for (int k = 0; k < kNarrowMax / 32; k++)
+            {
+                const int c = sh.warp_count[k];
+                base += k < warp ? c : 0;
+                total += c;
+            }
+            if (push >= 0)
+                qn[base + __popc(mask & ((1u << lane) - 1))] = push;
+            if (tid == 0)
+                sh.qn = total;
+        }
+        rounds++;
+        bids += n;
+        buf ^= 1;
+        NTICK(5);
+        __syncthreads();
+        NTICK(6);
+#ifdef B200LSAP_TIMING
+        {
+            // whole general round by number of bidders: 1-4, 5-8, 9-32, 33-256
+            const long long dt = clock64() - t_round;
+            if (n <= 4) { bk_c0 += dt; bk_r0++; }
+            else if (n <= 8) { bk_c1 += dt; bk_r1++; }
+            else if (n <= 32) { bk_c2 += dt; bk_r2++; }
+            else { bk_c3 += dt; bk_r3++; }
+        }
+#endif
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+        const bool finished = sh.qn == 0 && !sh.stop && ctrl->status == 0;
+        if (finished)
+        {
+            ctrl->count[cur] = 0;
+            if (ctrl->phase + 1 >= ctrl->n_phases)
+                ctrl->done = 1;
+        }
+        ctrl->rounds += rounds;
+        ctrl->bids += bids;
+        ctrl->narrow_rounds += rounds;
+        ctrl->cache_hits += bids - misses;
+        ctrl->cache_misses += misses;
+        ctrl->gs_bids += fast; // bids placed by the one-bidder path (included in rounds and bids)
+        if (sh.pmax > ctrl->pmax)
+            ctrl->pmax = sh.pmax;
+#ifdef B200LSAP_TIMING
+        ctrl->dbg[0] += clock64() - t_begin;
+        ctrl->dbg[8] += rounds;
+        ctrl->dbg[9] += bids;
+        ctrl->dbg[1] += fast;
+        ctrl->dbg[2] += acc2;
+        ctrl->dbg[3] += acc3;
+        ctrl->dbg[4] += acc4;
+        ctrl->dbg[5] += acc5;
+        ctrl->dbg[6] += acc6;
+        ctrl->dbg[7] += acc7;
+        ctrl->dbg[10] += bk_r0; ctrl->dbg[11] += bk_c0;
+        ctrl->dbg[12] += bk_r1; ctrl->dbg[13] += bk_c1;
+        ctrl->dbg[14] += bk_r2; ctrl->dbg[15] += bk_c2;
+        ctrl->dbg[4] = g_ev[0]; ctrl->dbg[6] = g_ev[1]; ctrl->dbg[12] = g_ev[2]; ctrl->dbg[13] = g_ev[3];
+#endif
+    }
+}
+
+} // namespace b200lsap

@@ -389,8 +389,10 @@ def main():
                        "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (a mid-size dense solve does not shard)",
                        "eps_final": solve_stats["eps_final"], "rounds": solve_stats["rounds"], "bids": solve_stats["bids"],
                        "phases": solve_stats["phases"], "narrow_rounds": solve_stats["narrow_rounds"],
-                       "tail_bids": solve_stats["tail_bids"],
-                       "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"] + solve_stats["tail_bids"], 1),
+                       "one_bidder_rounds": solve_stats["tail_bids"],
+                       "cache_hits": solve_stats["cache_hits"], "cache_misses": solve_stats["cache_misses"],
+                       "eps_first": solve_stats["eps_first"],
+                       "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"], 1),
                        "parity_vs_reference_golden": parity_note},
             "roofline": roofline,
             "solve_algorithmic_gbs": solve_gbs,

@@ -62,10 +62,10 @@ typedef struct
 {
     double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
     int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on */
-    double eps_start;      /* first eps of the scaling schedule; <= 0: default (fp32: a quarter of the mean
+    double eps_start;      /* first eps of the scaling schedule; <= 0: default (fp32: an eighth of the mean
                               spread of a row's best ~36 values, measured on sampled rows, at most 0.25;
                               fp64: 0.25).  Only the LAST phase, at eps_multiplier / cols, decides the result. */
-    double eps_factor;     /* eps is divided by this between phases; <= 1: default */
+    double eps_factor;     /* eps is divided by this between phases; <= 1: default (7) */
     int64_t max_rounds;    /* watchdog; <= 0: default */
     int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
                               of a round, driven from the host (profiling and cross-checks) */
@@ -91,7 +91,9 @@ typedef struct
     double ms_solve;   /* auction kernels only, CUDA events on the handle's stream */
     double ms_download;
     int64_t launches;  /* kernels launched by this call */
-    int64_t tail_bids; /* bids placed by the Gauss-Seidel tail (included in bids, not in rounds) */
+    int64_t tail_bids; /* fp32 with row caches: bids of one-bidder rounds (k_narrow's single-warp chain; included
+                          in bids and in rounds).  Row-scanning paths: bids placed by the Gauss-Seidel tail
+                          (included in bids, not in rounds) */
     int64_t tail_runs; /* times the tail took over */
     int64_t narrow_rounds; /* rounds run as narrow rounds (included in rounds) */
     int64_t cache_hits;    /* narrow-round bids answered from the row cache alone */

@@ -49,6 +49,14 @@ if __name__ == "__main__":
             print(f"sweep 16384^2: {ms:.4f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
+    if "c4f" in which:
+        for f in (3.0, 4.0, 5.0, 7.0, 10.0):
+            dense(16384, 16384, reps=1, eps_factor=f)
+    if "seeds" in which:
+        for f in (5.0, 7.0):
+            for n in (4096, 8192, 16384):
+                for seed in (1, 2, 3):
+                    dense(n, n, seed=seed, reps=1, eps_factor=f)
     if "c4t" in which:
         dense(16384, 16384, reps=2)
     if "c4n" in which:

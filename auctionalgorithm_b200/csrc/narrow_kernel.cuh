@@ -68,9 +68,25 @@ __device__ __forceinline__ double key_to_double(unsigned long long k)
 __device__ long long g_ev[8]; // developer counters of the one-bidder path
 #endif
 
+template <bool kSmem, bool kChase>
+__device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, const double* prices_s, const int* owner_s,
+                                                 const int2 e, const RowCacheHdr h, int lane, Top2<float>& t, int& prev,
+                                                 long long* evp);
+
 template <bool kSmem, bool kChase = false>
 __device__ __forceinline__ bool narrow_eval(const DenseState<float>& s, const double* prices_s, const int* owner_s,
                                             int i, int lane, Top2<float>& t, int& prev, long long* evp = nullptr)
+{
+    return narrow_eval_regs<kSmem, kChase>(s, prices_s, owner_s, s.cache[(long long)i * kCacheK + lane], s.cache_hdr[i],
+                                           lane, t, prev, evp);
+}
+
+// The same with the row's cache entry and header already loaded (one-bidder chain: the next
+// row's loads are issued before the current bid is committed).
+template <bool kSmem, bool kChase>
+__device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, const double* prices_s, const int* owner_s,
+                                                 const int2 e, const RowCacheHdr h, int lane, Top2<float>& t, int& prev,
+                                                 long long* evp)
 {
 #ifdef B200LSAP_TIMING
     long long ev0 = clock64();
@@ -88,8 +104,6 @@ __device__ __forceinline__ bool narrow_eval(const DenseState<float>& s, const do
 #else
 #define EVTICK(k, ...)
 #endif
-    const int2 e = s.cache[(long long)i * kCacheK + lane];
-    const RowCacheHdr h = s.cache_hdr[i];
     EVTICK(0, "r"(e.x), "r"(e.y), "r"(h.count));
     const float a = __int_as_float(e.y);
     double p;
@@ -106,14 +120,6 @@ __device__ __forceinline__ bool narrow_eval(const DenseState<float>& s, const do
     }
     EVTICK(1, "d"(p), "r"(own));
     const bool valid = a != 0.f && lane < h.count;
-    if (kChase && lane < 4 && valid && own >= 0)
-    {
-        // one-bidder chain: the next bidder is the owner of the column this row takes, most likely one
-        // of the row's best few columns; pull those owners' caches towards L1 while the top-2 is reduced
-        prefetch_l1(s.cache + (long long)own * kCacheK);
-        prefetch_l1(s.cache + (long long)own * kCacheK + kCacheK / 2);
-        prefetch_l1(s.cache_hdr + own);
-    }
     const unsigned long long key = valid ? ordered_key(widen_exact(a) - p) : 0ull;
     const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
     // best: max of the high words, then of the low words among those, then the lowest column
@@ -350,12 +356,21 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
 #else
                 long long* const evq = nullptr;
 #endif
+                int2 e = s.cache[(long long)i * kCacheK + lane];
+                RowCacheHdr h = s.cache_hdr[i];
                 for (;;)
                 {
                     Top2<float> t;
                     int prev;
-                    if (!narrow_eval<kSmem, true>(s, prices_s, owner_s, i, lane, t, prev, evq))
+                    if (!narrow_eval_regs<kSmem, true>(s, prices_s, owner_s, e, h, lane, t, prev, evq))
                         break; // the general round below scans the row
+                    // the evicted row bids next: its cache is requested before this bid is committed,
+                    // so the L2 latency of the load overlaps the stores
+                    if (prev >= 0)
+                    {
+                        e = s.cache[(long long)prev * kCacheK + lane];
+                        h = s.cache_hdr[prev];
+                    }
                     if (lane == 0)
                     {
                         const double bid = (double)t.a - t.w + eps; // Auction.h:250

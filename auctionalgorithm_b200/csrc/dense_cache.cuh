@@ -66,18 +66,26 @@ __device__ __forceinline__ float4 piece_f(const float4 a, const float4 q)
 // Every thread of the CTA.  Scans row i, rebuilds its cache, returns true when the result
 // (bs.v, bs.w, bs.j, bs.a) is exact; all threads see the same return value and may read bs until
 // the next call.  On false the row's cache is left empty.
-// kT = threads of the CTA (1024 in the persistent kernel, 512 in k_narrow).  The 64 threshold candidates
-// are the top-2 of 32 groups of kT / 32 consecutive threads (a warp, or half a warp).
-template <int kT>
-__device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, BuildShared& bs, int i, float margin)
+// kT = threads that share the row: the whole CTA (k_probe 1024, k_narrow 512; tid = threadIdx.x, barrier
+// 0), or a quarter of the persistent kernel's CTA (cache_build_sweep: 256 threads with a named barrier
+// of their own, four rows in flight per SM).  The 64 threshold candidates are the top-2 of 32 groups
+// of kT / 32 consecutive threads.  kBuildRegPieces pieces of the row stay in registers between the
+// two passes; the rest (all of it with 0) is read again, from L2.
+template <int kT> __device__ __forceinline__ void group_bar(int bar_id)
 {
-    constexpr int kBuildRegPieces = BuildRegPieces<kT>::value;
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(kT) : "memory");
+}
+
+template <int kT, int kBuildRegPieces = BuildRegPieces<kT>::value>
+__device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, BuildShared& bs, int i, float margin,
+                                               int tid = threadIdx.x, int bar_id = 0)
+{
     constexpr int kGroup = kT / 32; // lanes per candidate group
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int lane = tid & 31;
     const float* __restrict__ row = s.A + (long long)i * s.ld;
     const int c1 = s.cols4;
     constexpr int stride = 4 * kT;
-    float4 areg[kBuildRegPieces];
+    float4 areg[kBuildRegPieces > 0 ? kBuildRegPieces : 1];
     // ---- pass 1: f = a - (float)p, top-2 of the thread's elements -------------------------------
     float hi = -INFINITY, lo = -INFINITY;
 #pragma unroll
@@ -101,13 +109,29 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
             lo = fmaxf(lo, fminf(hi, f.w)), hi = fmaxf(hi, f.w);
         }
     }
-    for (int cc = tid * 4 + kBuildRegPieces * stride; cc < c1; cc += stride) // rows longer than 16384 columns
+    for (int c0 = tid * 4 + kBuildRegPieces * stride; c0 < c1; c0 += 4 * stride) // what registers do not hold
     {
-        const float4 f = piece_f(ld_stream4(row + cc), *reinterpret_cast<const float4*>(s.pricesf + cc));
-        lo = fmaxf(lo, fminf(hi, f.x)), hi = fmaxf(hi, f.x);
-        lo = fmaxf(lo, fminf(hi, f.y)), hi = fmaxf(hi, f.y);
-        lo = fmaxf(lo, fminf(hi, f.z)), hi = fmaxf(hi, f.z);
-        lo = fmaxf(lo, fminf(hi, f.w)), hi = fmaxf(hi, f.w);
+        float4 a4[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+        {
+            a4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c0 + u * stride < c1)
+                a4[u] = ld_stream4(row + c0 + u * stride);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+        {
+            const int cc = c0 + u * stride;
+            if (cc < c1)
+            {
+                const float4 f = piece_f(a4[u], *reinterpret_cast<const float4*>(s.pricesf + cc));
+                lo = fmaxf(lo, fminf(hi, f.x)), hi = fmaxf(hi, f.x);
+                lo = fmaxf(lo, fminf(hi, f.y)), hi = fmaxf(hi, f.y);
+                lo = fmaxf(lo, fminf(hi, f.z)), hi = fmaxf(hi, f.z);
+                lo = fmaxf(lo, fminf(hi, f.w)), hi = fmaxf(hi, f.w);
+            }
+        }
     }
 #pragma unroll
     for (int sft = kGroup / 2; sft >= 1; sft >>= 1)
@@ -129,7 +153,7 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         bs.T = INFINITY;
         bs.kth = -CUDART_INF;
     }
-    __syncthreads();
+    group_bar<kT>(bar_id);
     // ---- threshold: the r-th largest of the (up to) 64 candidates, r = 32 for a full CTA --------
     if (tid < 64)
     {
@@ -145,13 +169,13 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         if (finite >= 2 && rank == r - 1)
             bs.T = x - 2.f * margin;
     }
-    __syncthreads();
+    group_bar<kT>(bar_id);
     const float T = bs.T;
     if (!(T < INFINITY)) // fewer than two edges in the row
     {
         if (tid == 0)
             s.cache_hdr[i] = RowCacheHdr{0.0, 0, 0};
-        __syncthreads();
+        group_bar<kT>(bar_id);
         return false;
     }
     // ---- pass 2: compact the survivors ----------------------------------------------------------
@@ -177,31 +201,46 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
             }
         }
     }
-    for (int cc = tid * 4 + kBuildRegPieces * stride; cc < c1; cc += stride) // re-read from L2
+    for (int c0 = tid * 4 + kBuildRegPieces * stride; c0 < c1; c0 += 4 * stride) // re-read from L2, last use
     {
-        const float4 a4 = ld_stream4(row + cc);
-        const float4 f = piece_f(a4, *reinterpret_cast<const float4*>(s.pricesf + cc));
-        if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > T)
-        {
-            const float fv[4] = {f.x, f.y, f.z, f.w};
-            const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+        float4 a4[4];
 #pragma unroll
-            for (int e = 0; e < 4; e++)
-                if (fv[e] > T)
+        for (int u = 0; u < 4; u++)
+        {
+            a4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c0 + u * stride < c1)
+                a4[u] = ld_stream4_evict_first(row + c0 + u * stride);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+        {
+            const int cc = c0 + u * stride;
+            if (cc < c1)
+            {
+                const float4 f = piece_f(a4[u], *reinterpret_cast<const float4*>(s.pricesf + cc));
+                if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > T)
                 {
-                    const int slot = atomicAdd(&bs.cnt, 1);
-                    if (slot < kSurvCap)
-                        bs.surv[slot] = make_int2(cc + e, __float_as_int(av[e]));
+                    const float fv[4] = {f.x, f.y, f.z, f.w};
+                    const float av[4] = {a4[u].x, a4[u].y, a4[u].z, a4[u].w};
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        if (fv[e] > T)
+                        {
+                            const int slot = atomicAdd(&bs.cnt, 1);
+                            if (slot < kSurvCap)
+                                bs.surv[slot] = make_int2(cc + e, __float_as_int(av[e]));
+                        }
                 }
+            }
         }
     }
-    __syncthreads();
+    group_bar<kT>(bar_id);
     const int cnt = bs.cnt;
     if (cnt < 2 || cnt > kSurvCap)
     {
         if (tid == 0)
             s.cache_hdr[i] = RowCacheHdr{0.0, 0, 0};
-        __syncthreads();
+        group_bar<kT>(bar_id);
         return false;
     }
     // ---- exact values, ranks -----------------------------------------------------------------------
@@ -213,7 +252,7 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         d = widen_exact(__int_as_float(mine.y)) - s.prices[mine.x];
         bs.sval[tid] = d;
     }
-    __syncthreads();
+    group_bar<kT>(bar_id);
     if (tid < cnt)
     {
         int rank = 0;
@@ -237,7 +276,7 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
     }
     if (tid >= cnt && tid < kCacheK)
         s.cache[(long long)i * kCacheK + tid] = make_int2(0, 0); // a == 0: not an entry
-    __syncthreads();
+    group_bar<kT>(bar_id);
     const double bound_T = (double)T + (double)margin;
     const bool ok = bs.w > bound_T;
     if (tid == 0)
@@ -253,17 +292,20 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
-// All CTAs: a fresh cache for every row (entry of the narrow rounds of an eps phase).
-__device__ __noinline__ void cache_build_sweep(const DenseState<float>& s, BuildShared& bs, float margin)
+// All CTAs: a fresh cache for every row (entry of the narrow rounds of an eps phase).  A scan is a
+// chain of latencies (HBM, six barriers, two small rank loops: ~8 us when a whole CTA takes one row at
+// a time), so every CTA works on four rows at once: 256 threads and a named barrier per row, the
+// row read twice (HBM, then L2) instead of being held in registers.
+constexpr int kSweepGroupThreads = 256;
+constexpr int kSweepGroups = kThreads / kSweepGroupThreads;
+
+__device__ __noinline__ void cache_build_sweep(const DenseState<float>& s, BuildShared* bs, float margin)
 {
-    const unsigned row_bytes = (unsigned)(s.cols4 * sizeof(float));
-    const bool can_prefetch = (row_bytes & 15u) == 0 && ((s.ld * sizeof(float)) & 15u) == 0;
-    for (int i = blockIdx.x; i < s.rows; i += gridDim.x)
+    const int g = threadIdx.x / kSweepGroupThreads, gtid = threadIdx.x % kSweepGroupThreads;
+    for (int i = blockIdx.x * kSweepGroups + g; i < s.rows; i += gridDim.x * kSweepGroups)
     {
-        if (can_prefetch && threadIdx.x == 0 && i + (int)gridDim.x < s.rows)
-            prefetch_row_l2(s.A + (long long)(i + gridDim.x) * s.ld, row_bytes);
-        cta_scan_build<kThreads>(s, bs, i, margin);
-        __syncthreads();
+        cta_scan_build<kSweepGroupThreads, 0>(s, bs[g], i, margin, gtid, 1 + g);
+        group_bar<kSweepGroupThreads>(1 + g); // bs[g] is reused by the next row
     }
 }
 

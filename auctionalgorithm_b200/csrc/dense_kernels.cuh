@@ -889,12 +889,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     const long long n_threads = (long long)gridDim.x * kThreads;
     volatile DenseCtrl* ctrl = s.ctrl;
     __shared__ NarrowShared<T> narrow_sh;
-    __shared__ BuildShared build_sh;
+    __shared__ BuildShared build_sh[kSweepGroups];
 
     // The fp32 solve runs as one launch per eps phase (k_narrow finishes each phase's narrow rounds in
     // between, narrow_kernel.cuh): the loop state lives in the controller block across launches.
     if (ctrl->done || ctrl->status != 0)
         return;
+#ifdef B200LSAP_TIMING
+    const long long tk0 = clock64();
+#endif
     int cur = ctrl->cur;
     int phase = ctrl->phase;
     int seq = 0;        // CTA 0: sequence number of the last narrow round; scanners: last mailbox flag consumed
@@ -943,7 +946,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
                 {
                     // a fresh cache for every row, then this launch ends: k_narrow (one SM, prices in
                     // shared memory) finishes the phase, the next launch starts the next one
+#ifdef B200LSAP_TIMING
+                    const long long tb0 = clock64();
+#endif
                     cache_build_sweep(s, build_sh, filter_margin(amax, fmax(ctrl->pmax, amax)));
+#ifdef B200LSAP_TIMING
+                    if (tid == 0)
+                        s.ctrl->dbg[14] += clock64() - tb0;
+#endif
                     handed_over = true;
                     break;
                 }
@@ -985,6 +995,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
         ctrl->cur = cur;
         if (!handed_over)
             ctrl->done = 1;
+#ifdef B200LSAP_TIMING
+        s.ctrl->dbg[15] += clock64() - tk0;
+        s.ctrl->dbg[13] += rounds;
+#endif
     }
 }
 

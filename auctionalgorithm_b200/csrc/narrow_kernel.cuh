@@ -606,9 +606,6 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->dbg[6] += acc6;
         ctrl->dbg[7] += acc7;
         ctrl->dbg[10] += bk_r0; ctrl->dbg[11] += bk_c0;
-        ctrl->dbg[12] += bk_r1; ctrl->dbg[13] += bk_c1;
-        ctrl->dbg[14] += bk_r2; ctrl->dbg[15] += bk_c2;
-        ctrl->dbg[4] = g_ev[0]; ctrl->dbg[6] = g_ev[1]; ctrl->dbg[12] = g_ev[2]; ctrl->dbg[13] = g_ev[3];
 #endif
     }
 }

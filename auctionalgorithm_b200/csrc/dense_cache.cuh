@@ -296,7 +296,7 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // chain of latencies (HBM, six barriers, two small rank loops: ~8 us when a whole CTA takes one row at
 // a time), so every CTA works on four rows at once: 256 threads and a named barrier per row, the
 // row read twice (HBM, then L2) instead of being held in registers.
-constexpr int kSweepGroupThreads = 256;
+constexpr int kSweepGroupThreads = 128;
 constexpr int kSweepGroups = kThreads / kSweepGroupThreads;
 
 __device__ __noinline__ void cache_build_sweep(const DenseState<float>& s, BuildShared* bs, float margin)

@@ -469,10 +469,15 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                 // columns first (match.any costs ~11 cycles per distinct value on sm_100: 370 for 32
                 // distinct columns); only a round with a contested column compares bids
                 bool dup = false;
-                for (int k = 0; k < n; k++)
+                for (int k0 = 0; k0 < n; k0 += 4) // four independent shuffles in flight
                 {
-                    const int oc = __shfl_sync(kFullMask, my_col, k);
-                    dup |= oc == my_col && k != lane;
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                    {
+                        const int k = k0 + u;
+                        const int oc = __shfl_sync(kFullMask, my_col, k & 31);
+                        dup |= k < n && oc == my_col && k != lane;
+                    }
                 }
                 bool win = act;
                 if (__any_sync(kFullMask, dup))
@@ -487,13 +492,6 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                 NTICK(7);
                 if (win)
                 {
-                    if (my_prev >= 0)
-                    {
-                        // the evicted row bids next round: start pulling its cache towards this SM
-                        prefetch_l1(s.cache + (long long)my_prev * kCacheK);
-                        prefetch_l1(s.cache + (long long)my_prev * kCacheK + kCacheK / 2);
-                        prefetch_l1(s.cache_hdr + my_prev);
-                    }
                     narrow_commit<kSmem>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
                     if (my_bid > sh.pmax)
                         atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),

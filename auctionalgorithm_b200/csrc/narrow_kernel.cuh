@@ -229,7 +229,10 @@ __device__ __noinline__ void narrow_misses(const DenseState<float>& s, NarrowKSh
     }
 }
 
-// price / lock / evict of one winning bid (Auction.h:259-270), shared-memory mirror first
+// price / lock / evict of one winning bid (Auction.h:259-270).  With prices and owners in shared
+// memory nothing goes to global memory here: the same few lines would be stored to round after round
+// (a price war hits the same columns), and those stores cost the general round ~340 cycles (measured).
+// narrow_writeback publishes the state at the end of the kernel, and before any row scan.
 template <bool kSmem>
 __device__ __forceinline__ void narrow_commit(const DenseState<float>& s, double* prices_s, int* owner_s, int row, int col,
                                               double bid, int prev)
@@ -239,12 +242,42 @@ __device__ __forceinline__ void narrow_commit(const DenseState<float>& s, double
         prices_s[col] = bid;
         owner_s[col] = row;
     }
-    s.prices[col] = bid;
-    s.pricesf[col] = (float)bid;
-    s.owner[col] = row;
-    s.row2col[row] = col;
-    if (prev >= 0)
-        s.row2col[prev] = -1;
+    else
+    {
+        s.prices[col] = bid;
+        s.pricesf[col] = (float)bid;
+        s.owner[col] = row;
+        s.row2col[row] = col;
+        if (prev >= 0)
+            s.row2col[prev] = -1;
+    }
+}
+
+// Every thread: global prices / pricesf / owner from the shared-memory copies (barrier included).
+__device__ __forceinline__ void narrow_flush_prices(const DenseState<float>& s, const double* prices_s, const int* owner_s)
+{
+    for (int j = threadIdx.x; j < s.cols; j += kNarrowThreads)
+    {
+        const double p = prices_s[j];
+        s.prices[j] = p;
+        s.pricesf[j] = (float)p;
+        s.owner[j] = owner_s[j];
+    }
+    __syncthreads();
+}
+
+// Every thread, end of the kernel: prices, owners, and row2col rebuilt as the inverse of owner.
+__device__ __forceinline__ void narrow_writeback(const DenseState<float>& s, const double* prices_s, const int* owner_s)
+{
+    for (int i = threadIdx.x; i < s.rows; i += kNarrowThreads)
+        s.row2col[i] = -1;
+    narrow_flush_prices(s, prices_s, owner_s);
+    for (int j = threadIdx.x; j < s.cols; j += kNarrowThreads)
+    {
+        const int o = owner_s[j];
+        if (o >= 0)
+            s.row2col[o] = j;
+    }
 }
 
 template <bool kSmem>
@@ -447,6 +480,8 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         const int nmiss = sh.nmiss;
         if (nmiss > 0)
         {
+            if (kSmem)
+                narrow_flush_prices(s, prices_s, owner_s); // the row scans read prices from global memory
             narrow_misses<kSmem>(s, sh, owner_s, q, n, eps, amax); // ends with a barrier
             if (tid == 0)
                 sh.nmiss = 0;
@@ -575,6 +610,8 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
 #endif
     }
     __syncthreads();
+    if (kSmem)
+        narrow_writeback(s, prices_s, owner_s);
     if (tid == 0)
     {
         const bool finished = sh.qn == 0 && !sh.stop && ctrl->status == 0;

@@ -780,8 +780,46 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     const int64_t resident = (int64_t)per_sm * h->num_sms;
     if (grid > resident)
         grid = resident;
+    // B200LSAP_BATCH_SMEM=1: the shared-memory kernel (k_auction_batch); B200LSAP_BATCH_WARPS=16|24|32: warps per
+    // SM the streaming kernel is compiled for (developer A/B knobs)
+    static const bool smem_mode = getenv("B200LSAP_BATCH_SMEM") && atoi(getenv("B200LSAP_BATCH_SMEM")) != 0;
+    static const int warps_mode = getenv("B200LSAP_BATCH_WARPS") ? atoi(getenv("B200LSAP_BATCH_WARPS")) : 32;
     CU(cudaEventRecord(h->ev[1], h->stream));
-    kernel<<<(int)grid, 32, smem, h->stream>>>(P);
+    if (!smem_mode)
+    {
+        // lanes per problem: 8 (columns per lane <= 8) or 4 (columns per lane <= 16)
+        static const int lanes_mode = getenv("B200LSAP_BATCH_LANES") ? atoi(getenv("B200LSAP_BATCH_LANES")) : 4;
+        if (lanes_mode == 4)
+        {
+#define B200LSAP_STREAM4(C) k_auction_batch_stream<C, 4, 20>
+            static const BatchKernel k4[16] = {B200LSAP_STREAM4(1),  B200LSAP_STREAM4(2),  B200LSAP_STREAM4(3),
+                                               B200LSAP_STREAM4(4),  B200LSAP_STREAM4(5),  B200LSAP_STREAM4(6),
+                                               B200LSAP_STREAM4(7),  B200LSAP_STREAM4(8),  B200LSAP_STREAM4(9),
+                                               B200LSAP_STREAM4(10), B200LSAP_STREAM4(11), B200LSAP_STREAM4(12),
+                                               B200LSAP_STREAM4(13), B200LSAP_STREAM4(14), B200LSAP_STREAM4(15),
+                                               B200LSAP_STREAM4(16)};
+            int64_t sgrid = (batch + 7) / 8;
+            sgrid = std::min<int64_t>(sgrid, (int64_t)20 * h->num_sms);
+            k4[(cols + 3) / 4 - 1]<<<(int)sgrid, 32, 0, h->stream>>>(P);
+        }
+        else
+        {
+#define B200LSAP_STREAM_TABLE(W)                                                                                   \
+    {k_auction_batch_stream<1, 8, W>, k_auction_batch_stream<2, 8, W>, k_auction_batch_stream<3, 8, W>,             \
+     k_auction_batch_stream<4, 8, W>, k_auction_batch_stream<5, 8, W>, k_auction_batch_stream<6, 8, W>,             \
+     k_auction_batch_stream<7, 8, W>, k_auction_batch_stream<8, 8, W>}
+            static const BatchKernel k16[kBatchColsPerLane] = B200LSAP_STREAM_TABLE(16);
+            static const BatchKernel k24[kBatchColsPerLane] = B200LSAP_STREAM_TABLE(24);
+            static const BatchKernel k32[kBatchColsPerLane] = B200LSAP_STREAM_TABLE(32);
+            const int kW = warps_mode == 16 ? 16 : (warps_mode == 24 ? 24 : 32);
+            const BatchKernel* tab = kW == 16 ? k16 : (kW == 32 ? k32 : k24);
+            int64_t sgrid = (batch + kBatchPerWarp - 1) / kBatchPerWarp;
+            sgrid = std::min<int64_t>(sgrid, (int64_t)kW * h->num_sms);
+            tab[(cols + kBatchGroup - 1) / kBatchGroup - 1]<<<(int)sgrid, 32, 0, h->stream>>>(P);
+        }
+    }
+    else
+        kernel<<<(int)grid, 32, smem, h->stream>>>(P);
     h->launches++;
     CU(cudaEventRecord(h->ev[2], h->stream));
     CU(cudaMemcpyAsync(&h->h_ctrl->status, P.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));

@@ -415,6 +415,8 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->eps_factor = plan.eps_factor;
     hc->eps_final = plan.eps.back();
     hc->eps_probe_scale = h->eps_probe_scale;
+    hc->eps_cap = 0.25;
+    hc->phase_budget = eps_auto ? 4 * plan.rows + 1024 : 0;
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
     s.use_cache = (sizeof(T) == 4 && plan.driver == 0 && plan.use_cache) ? 1 : 0;
     std::vector<double> eps = plan.eps;
@@ -466,16 +468,31 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
                 const bool smem_prices = dyn + fa.sharedSizeBytes + 1024 <= (size_t)optin;
                 if (smem_prices)
                     CU(cudaFuncSetAttribute(k_narrow<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-                for (int p = 0; p < n_phases; p++)
+                // one batch of launches covers the schedule; only an escalated schedule (escalate_schedule)
+                // needs another one
+                for (int batch_no = 0; batch_no < 64; batch_no++)
                 {
-                    CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads), args,
-                                                   0, h->stream));
-                    if (smem_prices)
-                        k_narrow<true><<<1, kNarrowThreads, dyn, h->stream>>>(s);
-                    else
-                        k_narrow<false><<<1, kNarrowThreads, 0, h->stream>>>(s);
-                    h->launches += 2;
+                    for (int p = 0; p < n_phases; p++)
+                    {
+                        CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads),
+                                                       args, 0, h->stream));
+                        if (smem_prices)
+                            k_narrow<true><<<1, kNarrowThreads, dyn, h->stream>>>(s);
+                        else
+                            k_narrow<false><<<1, kNarrowThreads, 0, h->stream>>>(s);
+                        h->launches += 2;
+                    }
+                    CU(cudaEventRecord(h->ev[2], h->stream));
+                    CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
+                    CU(cudaStreamSynchronize(h->stream));
+                    if (hc->done || hc->status != 0)
+                        break;
+                    n_phases = hc->n_phases - (hc->phase < 0 ? 0 : hc->phase);
+                    if (n_phases < 1)
+                        n_phases = 1;
                 }
+                if (!hc->done && hc->status == 0)
+                    hc->status = B200LSAP_ERR_MAX_ROUNDS;
             }
         }
         else
@@ -542,7 +559,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         stats->phases = hc->phase + 1;
         stats->narrow_rounds = hc->narrow_rounds;
         stats->tail_bids = hc->gs_bids;
-        stats->tail_runs = hc->gs_episodes;
+        stats->tail_runs = hc->gs_episodes + hc->escalations;
         stats->bid_bytes = hc->bids * plan.cols * (int64_t)sizeof(T);
         stats->eps_final = plan.eps.back();
         stats->eps_first = hc->eps[0];

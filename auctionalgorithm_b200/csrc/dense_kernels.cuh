@@ -906,8 +906,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     const long long max_rounds = ctrl->max_rounds - ctrl->rounds;
     long long rounds = 0, bids = 0;
     NarrowCounts ncnt{0, 0, 0, 0};
-    double eps = ctrl->eps[phase];
+    double eps = ctrl->eps[phase < 0 ? 0 : phase]; // phase == -1: k_narrow restarted the schedule (escalate_schedule)
     const double amax = ctrl->amax;
+    long long phase_rounds = 0; // wide rounds of the current phase in this launch
     const bool cached = sizeof(T) == 4 && s.use_cache;
     const int narrow_rows = cached ? min(s.narrow_rows, kNarrowMax) : min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
     bool handed_over = false;
@@ -922,10 +923,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
                 break;
             phase++;
             eps = ctrl->eps[phase];
+            phase_rounds = 0;
             grid.sync(); // everybody has read count[cur] == 0 before it is overwritten
             reset_phase(s, s.list[cur], tid, n_threads);
             if (tid == 0)
+            {
                 ctrl->count[cur] = s.rows;
+                ctrl->phase_work = 0;
+            }
             grid.sync();
             continue;
         }
@@ -982,10 +987,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
         grid.sync();
         cur ^= 1;
         rounds++;
+        phase_rounds++;
         bids += n;
     }
     if (tid == 0)
     {
+        ctrl->phase_work += phase_rounds;
         ctrl->rounds += rounds + ncnt.rounds;
         ctrl->bids += bids + ncnt.bids + ncnt.gs_bids;
         ctrl->narrow_rounds += ncnt.rounds;
@@ -1077,6 +1084,9 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         s.ctrl->narrow_rounds = s.ctrl->gs_bids = s.ctrl->gs_episodes = 0;
         s.ctrl->cur = 0;
         s.ctrl->done = 0;
+        s.ctrl->phase_work = 0;
+        s.ctrl->escalations = 0;
+        s.ctrl->esc_phase = 0;
         s.narrow->arrived = 0u;
     }
     if (tid < kNarrowMax)

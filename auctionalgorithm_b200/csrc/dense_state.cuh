@@ -54,7 +54,16 @@ struct DenseCtrl
     int pad1;
     double eps_factor;
     double eps_final;
-    double eps_probe_scale; // eps[0] = this fraction of the mean probe spread (default 1/4)
+    double eps_probe_scale; // eps[0] = this fraction of the mean probe spread (default 1/8)
+    // safeguard of the data-sized start (narrow_kernel.cuh, escalate_schedule): the first phase of the
+    // schedule may spend phase_budget work units (rounds + 4 per cache miss); beyond that its eps was too
+    // small for this input and the schedule restarts from eps * factor^2 (at most eps_cap), prices kept
+    long long phase_work;   // work units of the current phase so far
+    long long phase_budget; // 0: no safeguard (explicit eps_start, fixed eps)
+    long long escalations;
+    int esc_phase;          // index of the first phase of the current schedule
+    int pad2;
+    double eps_cap;
     double probe[kProbeRows]; // best minus cache bound of the sampled rows at the initial prices, < 0: no sample
     double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)

@@ -280,6 +280,33 @@ __device__ __forceinline__ void narrow_writeback(const DenseState<float>& s, con
     }
 }
 
+// Safeguard of the data-sized first eps (k_probe / k_schedule).  The probe sizes eps[0] by the spread of a
+// row's best values; on inputs whose equilibrium prices are far larger than that spread (every row
+// wants the same few columns: a = u_i * v_j; or rows with very few edges) the first phase would crawl
+// there in steps of eps.  The first phase of the schedule therefore has a work budget (rounds + 4 per
+// cache miss, a few times the number of rows); when it is spent the schedule restarts from
+// eps * factor^2 (at most eps_cap, the classic start), prices kept, and that phase gets a budget again.
+// Only the last phase, at the reference's eps, decides the result, so any such restart is legal.
+__device__ __forceinline__ void escalate_schedule(DenseCtrl* ctrl, int cur)
+{
+    const int k = ctrl->phase;
+    const double f = ctrl->eps_factor;
+    double e = fmin(ctrl->eps_cap, ctrl->eps[k] * f * f);
+    int n = k;
+    while (e > ctrl->eps_final * 1.0000001 && n < kMaxPhases - 1)
+    {
+        ctrl->eps[n++] = e;
+        e /= f;
+    }
+    ctrl->eps[n++] = ctrl->eps_final;
+    ctrl->n_phases = n;
+    ctrl->esc_phase = k;
+    ctrl->phase = k - 1; // the next cooperative launch advances to phase k and resets the assignment
+    ctrl->count[cur] = 0;
+    ctrl->phase_work = 0;
+    ctrl->escalations++;
+}
+
 template <bool kSmem>
 __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_constant__ DenseState<float> s)
 {
@@ -344,6 +371,10 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
     }
     __syncthreads();
     int rounds = 0, buf = 0;
+    const bool esc_ok = ctrl->phase_budget > 0 && ctrl->phase == ctrl->esc_phase && eps < ctrl->eps_cap;
+    const long long work_budget = ctrl->phase_budget;
+    long long work = ctrl->phase_work; // the wide rounds of this phase
+    bool escalated = false;
     long long bids = 0, misses = 0, fast = 0;
 #ifdef B200LSAP_TIMING
     long long acc2 = 0, acc3 = 0, acc4 = 0, acc5 = 0, acc6 = 0, acc7 = 0;
@@ -358,6 +389,11 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         {
             if (tid == 0)
                 ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS
+            break;
+        }
+        if (esc_ok && work > work_budget)
+        {
+            escalated = true; // the same for every thread
             break;
         }
         int* const q = sh.q[buf];
@@ -419,7 +455,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                         break;
                     }
                     i = prev;
-                    if (rounds + served >= budget)
+                    if (rounds + served >= budget || (esc_ok && work + served > work_budget))
                         break;
                     __syncwarp(); // lane 0's shared-memory prices before the next gather
                 }
@@ -440,8 +476,9 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             rounds += served;
             bids += served;
             fast += served;
+            work += served;
             n = sh.qn;
-            if (n == 0 || rounds >= budget)
+            if (n == 0 || rounds >= budget || (esc_ok && work > work_budget))
             {
                 __syncthreads(); // sh.served is rewritten by the next fast episode
                 continue;
@@ -488,7 +525,9 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             if (sh.stop)
                 break;
             misses += nmiss;
+            work += 4 * nmiss;
         }
+        work++;
         // ---- resolve: highest bid per column, lowest row among equal bids ------------------------------
         if (n <= 32)
         {
@@ -621,6 +660,10 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             if (ctrl->phase + 1 >= ctrl->n_phases)
                 ctrl->done = 1;
         }
+        else if (escalated && ctrl->status == 0)
+            escalate_schedule(ctrl, cur);
+        else
+            ctrl->phase_work = work;
         ctrl->rounds += rounds;
         ctrl->bids += bids;
         ctrl->narrow_rounds += rounds;

@@ -94,7 +94,8 @@ typedef struct
     int64_t tail_bids; /* fp32 with row caches: bids of one-bidder rounds (k_narrow's single-warp chain; included
                           in bids and in rounds).  Row-scanning paths: bids placed by the Gauss-Seidel tail
                           (included in bids, not in rounds) */
-    int64_t tail_runs; /* times the tail took over */
+    int64_t tail_runs; /* row-scanning paths: times the tail took over.  fp32 with row caches: times the
+                          data-sized schedule was restarted from a larger eps (first phase over budget) */
     int64_t narrow_rounds; /* rounds run as narrow rounds (included in rounds) */
     int64_t cache_hits;    /* narrow-round bids answered from the row cache alone */
     int64_t cache_misses;  /* narrow-round bids that re-scanned their row (and rebuilt its cache) */

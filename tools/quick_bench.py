@@ -57,6 +57,20 @@ if __name__ == "__main__":
             for n in (4096, 8192, 16384):
                 for seed in (1, 2, 3):
                     dense(n, n, seed=seed, reps=1, eps_factor=f)
+    if "struct" in which:
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+        import test_gpu_structured as tg
+        for gen in tg.GENERATORS:
+            a = np.ascontiguousarray(gen(np.random.default_rng(7), 2048, 2048))
+            for opt in (dict(), dict(eps_start=0.25), dict(row_cache=-1, eps_start=0.25)):
+                t0 = time.time()
+                try:
+                    r2c, _ = h.solve(a, want_prices=True, max_rounds=3000000, **opt)
+                    st = h.last_stats
+                    print(f"{gen.__name__:16s} {str(opt):42s}: {st['ms_solve']:9.2f} ms rounds {st['rounds']:8d} phases {st['phases']:2d} "
+                          f"hit/miss {st['cache_hits']}/{st['cache_misses']} eps0 {st['eps_first']:.3g} restarts {st['tail_runs']}", flush=True)
+                except Exception as e:
+                    print(f"{gen.__name__:16s} {str(opt):42s}: FAILED after {time.time()-t0:.1f} s: {e}", flush=True)
     if "c4t" in which:
         dense(16384, 16384, reps=2)
     if "c4n" in which:

@@ -327,6 +327,9 @@ def main():
         sweep_ms.append(ms)
     sweep = statistics.mean(sweep_ms[3:])
     peak, peak_src = peaks()
+    # north_star's third quantity is the HBM bandwidth of the BIDDING kernel, the one kernel of the solve that
+    # streams the matrix (one fp32 row per bid); the rest of a square solve is latency-bound narrow rounds
+    # (k_narrow, one SM, reported as us_per_round / narrow_rounds in config), which no bandwidth roofline bounds
     roofline = {"bound": "hbm", "kernel": "k_bid<float> (bidding phase of a wide round, every row bids once)",
                 "achieved": nbytes / sweep / 1e6, "peak": peak, "unit": "GB/s",
                 "frac": nbytes / sweep / 1e6 / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
@@ -389,7 +392,7 @@ def main():
                        "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (a mid-size dense solve does not shard)",
                        "eps_final": solve_stats["eps_final"], "rounds": solve_stats["rounds"], "bids": solve_stats["bids"],
                        "phases": solve_stats["phases"], "narrow_rounds": solve_stats["narrow_rounds"],
-                       "one_bidder_rounds": solve_stats["tail_bids"],
+                       "one_bidder_rounds": solve_stats["tail_bids"], "schedule_restarts": solve_stats["tail_runs"],
                        "cache_hits": solve_stats["cache_hits"], "cache_misses": solve_stats["cache_misses"],
                        "eps_first": solve_stats["eps_first"],
                        "us_per_round": 1e3 * solve_stats["ms_solve"] / max(solve_stats["rounds"], 1),

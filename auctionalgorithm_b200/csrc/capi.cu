@@ -322,11 +322,8 @@ template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t 
     CU(h->prices.ensure((ldp + 512) * sizeof(double)));
     CU(h->pricesf.ensure((ldp + 512) * sizeof(float)));
     CU(h->cand.ensure((size_t)rows * kCand * sizeof(int2)));
-    if (sizeof(T) == 4)
-    {
-        CU(h->cache.ensure((size_t)rows * kCacheK * sizeof(int2)));
-        CU(h->cache_hdr.ensure((size_t)rows * sizeof(RowCacheHdr)));
-    }
+    CU(h->cache.ensure((size_t)rows * kCacheK * sizeof(CacheEnt<T>)));
+    CU(h->cache_hdr.ensure((size_t)rows * sizeof(RowCacheHdr)));
     CU(h->narrow.ensure(sizeof(NarrowCtrl)));
     CU(h->profits.ensure(rows * sizeof(double)));
     CU(h->slots.ensure(cols * sizeof(BidSlot)));
@@ -353,8 +350,8 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.prices = h->prices.as<double>();
     s.pricesf = h->pricesf.as<float>();
     s.cand = h->cand.as<int2>();
-    s.cache = sizeof(T) == 4 ? h->cache.as<int2>() : nullptr;
-    s.cache_hdr = sizeof(T) == 4 ? h->cache_hdr.as<RowCacheHdr>() : nullptr;
+    s.cache = h->cache.as<CacheEnt<T>>();
+    s.cache_hdr = h->cache_hdr.as<RowCacheHdr>();
     s.use_cache = 0;
     s.narrow = h->narrow.as<NarrowCtrl>();
     s.narrow_rows = 0;
@@ -410,7 +407,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->max_rounds = plan.max_rounds;
     for (size_t k = 0; k < plan.eps.size(); k++)
         hc->eps[k] = plan.eps[k];
-    const bool eps_auto = plan.eps_auto && sizeof(T) == 4;
+    const bool eps_auto = plan.eps_auto;
     hc->eps_auto = eps_auto ? 1 : 0;
     hc->eps_factor = plan.eps_factor;
     hc->eps_final = plan.eps.back();
@@ -418,7 +415,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->eps_cap = 0.25;
     hc->phase_budget = eps_auto ? 4 * plan.rows + 1024 : 0;
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
-    s.use_cache = (sizeof(T) == 4 && plan.driver == 0 && plan.use_cache) ? 1 : 0;
+    s.use_cache = (plan.driver == 0 && plan.use_cache) ? 1 : 0;
     std::vector<double> eps = plan.eps;
 
     CU(cudaEventRecord(h->ev[1], h->stream));
@@ -426,13 +423,12 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     k_absmax<T><<<grid_for(h, plan.rows * (int64_t)(s.cols4 / 4), 256 * 8), 256, 0, h->stream>>>(s.A, s.ld, s.rows, s.cols4,
                                                                                          s.ctrl);
     h->launches += 2;
-    if constexpr (sizeof(T) == 4)
     {
         if (eps_auto)
         {
             // first eps of the schedule from the data (dense_cache.cuh)
             const int n_probe = (int)std::min<int64_t>(kProbeRows, plan.rows);
-            k_probe<<<n_probe, kThreads, 0, h->stream>>>(s);
+            k_probe<T><<<n_probe, kThreads, 0, h->stream>>>(s);
             k_schedule<<<1, 32, 0, h->stream>>>(s.ctrl, n_probe);
             h->launches += 2;
             if (plan.driver != 0)
@@ -448,10 +444,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
         void* args[] = {&s};
         if (s.use_cache)
         {
-            // fp32 with row caches: per eps phase one cooperative launch (wide rounds, then a fresh cache
+            // row caches: per eps phase one cooperative launch (wide rounds, then a fresh cache
             // for every row) and one k_narrow launch (the narrow rounds on one SM, narrow_kernel.cuh),
             // all enqueued now; launches that find nothing left to do return at once.
-            if constexpr (sizeof(T) == 4)
             {
                 int n_phases = (int)eps.size();
                 if (eps_auto)
@@ -462,12 +457,12 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
                 }
                 const size_t dyn = (size_t)round_up(plan.cols, 2) * sizeof(double) + (size_t)plan.cols * sizeof(int);
                 cudaFuncAttributes fa;
-                CU(cudaFuncGetAttributes(&fa, k_narrow<true>));
+                CU(cudaFuncGetAttributes(&fa, k_narrow<true, T>));
                 int optin = 0;
                 CU(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
                 const bool smem_prices = dyn + fa.sharedSizeBytes + 1024 <= (size_t)optin;
                 if (smem_prices)
-                    CU(cudaFuncSetAttribute(k_narrow<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+                    CU(cudaFuncSetAttribute(k_narrow<true, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
                 // one batch of launches covers the schedule; only an escalated schedule (escalate_schedule)
                 // needs another one
                 for (int batch_no = 0; batch_no < 64; batch_no++)
@@ -477,9 +472,9 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
                         CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads),
                                                        args, 0, h->stream));
                         if (smem_prices)
-                            k_narrow<true><<<1, kNarrowThreads, dyn, h->stream>>>(s);
+                            k_narrow<true, T><<<1, kNarrowThreads, dyn, h->stream>>>(s);
                         else
-                            k_narrow<false><<<1, kNarrowThreads, 0, h->stream>>>(s);
+                            k_narrow<false, T><<<1, kNarrowThreads, 0, h->stream>>>(s);
                         h->launches += 2;
                     }
                     CU(cudaEventRecord(h->ev[2], h->stream));

@@ -214,6 +214,23 @@ __device__ __forceinline__ double4_t ld_stream4(const double* p)
     return r;
 }
 
+__device__ __forceinline__ double4_t ld_stream4_evict_first(const double* p)
+{
+    double4_t r;
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+                 : "=d"(r.x), "=d"(r.y)
+                 : "l"(p), "l"(pol));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+                 : "=d"(r.z), "=d"(r.w)
+                 : "l"(p + 2), "l"(pol));
+    return r;
+}
+
+// exact widening of a coefficient of either type
+__device__ __forceinline__ double widen_exact(double a) { return a; }
+
 template <typename T> struct Vec4;
 template <> struct Vec4<float>
 {

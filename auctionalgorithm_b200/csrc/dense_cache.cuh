@@ -38,16 +38,16 @@
 namespace b200lsap
 {
 
-struct BuildShared
+template <typename T> struct BuildShared
 {
-    float cand[64];        // warp w: cand[w] = largest f of its elements, cand[32 + w] = second largest
-    int2 surv[kSurvCap];   // survivors: (column, bits of a)
-    double sval[kSurvCap]; // their exact values
+    float cand[64];             // group g: cand[g] = largest f of its elements, cand[32 + g] = second largest
+    CacheEnt<T> surv[kSurvCap]; // survivors: (column, a)
+    double sval[kSurvCap];      // their exact values
     int cnt;
     int ok;
-    float T;
+    float thr; // the selection threshold
     int j;
-    float a;
+    T a;
     double v, w, kth;
 };
 
@@ -57,10 +57,19 @@ template <int kT> struct BuildRegPieces
     static constexpr int value = 4096 / kT;
 };
 
-__device__ __forceinline__ float4 piece_f(const float4 a, const float4 q)
+// f = fl32(a) - fl32(p) of one 4-element piece; a == 0 is "no edge".  For fp64 coefficients the
+// conversion adds at most 2^-24 |a| to the filter's error, still well inside filter_margin.
+template <typename V4> __device__ __forceinline__ float4 piece_f(const V4 a, const float4 q)
 {
-    return make_float4(a.x != 0.f ? a.x - q.x : -INFINITY, a.y != 0.f ? a.y - q.y : -INFINITY,
-                       a.z != 0.f ? a.z - q.z : -INFINITY, a.w != 0.f ? a.w - q.w : -INFINITY);
+    return make_float4(a.x != 0 ? (float)a.x - q.x : -INFINITY, a.y != 0 ? (float)a.y - q.y : -INFINITY,
+                       a.z != 0 ? (float)a.z - q.z : -INFINITY, a.w != 0 ? (float)a.w - q.w : -INFINITY);
+}
+
+template <typename T> __device__ __forceinline__ typename Vec4<T>::type vec4_zero()
+{
+    typename Vec4<T>::type v;
+    v.x = v.y = v.z = v.w = T(0);
+    return v;
 }
 
 // Every thread of the CTA.  Scans row i, rebuilds its cache, returns true when the result
@@ -76,23 +85,24 @@ template <int kT> __device__ __forceinline__ void group_bar(int bar_id)
     asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(kT) : "memory");
 }
 
-template <int kT, int kBuildRegPieces = BuildRegPieces<kT>::value>
-__device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, BuildShared& bs, int i, float margin,
+template <int kT, int kBuildRegPieces, typename T>
+__device__ __forceinline__ bool cta_scan_build(const DenseState<T>& s, BuildShared<T>& bs, int i, float margin,
                                                int tid = threadIdx.x, int bar_id = 0)
 {
+    using V4 = typename Vec4<T>::type;
     constexpr int kGroup = kT / 32; // lanes per candidate group
     const int lane = tid & 31;
-    const float* __restrict__ row = s.A + (long long)i * s.ld;
+    const T* __restrict__ row = s.A + (long long)i * s.ld;
     const int c1 = s.cols4;
     constexpr int stride = 4 * kT;
-    float4 areg[kBuildRegPieces > 0 ? kBuildRegPieces : 1];
+    V4 areg[kBuildRegPieces > 0 ? kBuildRegPieces : 1];
     // ---- pass 1: f = a - (float)p, top-2 of the thread's elements -------------------------------
     float hi = -INFINITY, lo = -INFINITY;
 #pragma unroll
     for (int u = 0; u < kBuildRegPieces; u++)
     {
         const int cc = tid * 4 + u * stride;
-        areg[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        areg[u] = vec4_zero<T>();
         if (cc < c1)
             areg[u] = ld_stream4_evict_first(row + cc);
     }
@@ -111,11 +121,11 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
     }
     for (int c0 = tid * 4 + kBuildRegPieces * stride; c0 < c1; c0 += 4 * stride) // what registers do not hold
     {
-        float4 a4[4];
+        V4 a4[4];
 #pragma unroll
         for (int u = 0; u < 4; u++)
         {
-            a4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            a4[u] = vec4_zero<T>();
             if (c0 + u * stride < c1)
                 a4[u] = ld_stream4(row + c0 + u * stride);
         }
@@ -150,7 +160,7 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
     {
         bs.cnt = 0;
         bs.ok = 0;
-        bs.T = INFINITY;
+        bs.thr = INFINITY;
         bs.kth = -CUDART_INF;
     }
     group_bar<kT>(bar_id);
@@ -167,11 +177,11 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         }
         const int r = min(32, max(2, (finite + 1) / 2));
         if (finite >= 2 && rank == r - 1)
-            bs.T = x - 2.f * margin;
+            bs.thr = x - 2.f * margin;
     }
     group_bar<kT>(bar_id);
-    const float T = bs.T;
-    if (!(T < INFINITY)) // fewer than two edges in the row
+    const float thr = bs.thr;
+    if (!(thr < INFINITY)) // fewer than two edges in the row
     {
         if (tid == 0)
             s.cache_hdr[i] = RowCacheHdr{0.0, 0, 0};
@@ -186,28 +196,28 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         if (cc < c1)
         {
             const float4 f = piece_f(areg[u], *reinterpret_cast<const float4*>(s.pricesf + cc));
-            if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > T)
+            if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > thr)
             {
                 const float fv[4] = {f.x, f.y, f.z, f.w};
-                const float av[4] = {areg[u].x, areg[u].y, areg[u].z, areg[u].w};
+                const T av[4] = {areg[u].x, areg[u].y, areg[u].z, areg[u].w};
 #pragma unroll
                 for (int e = 0; e < 4; e++)
-                    if (fv[e] > T)
+                    if (fv[e] > thr)
                     {
                         const int slot = atomicAdd(&bs.cnt, 1);
                         if (slot < kSurvCap)
-                            bs.surv[slot] = make_int2(cc + e, __float_as_int(av[e]));
+                            bs.surv[slot] = make_ent<T>(cc + e, av[e]);
                     }
             }
         }
     }
     for (int c0 = tid * 4 + kBuildRegPieces * stride; c0 < c1; c0 += 4 * stride) // re-read from L2, last use
     {
-        float4 a4[4];
+        V4 a4[4];
 #pragma unroll
         for (int u = 0; u < 4; u++)
         {
-            a4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            a4[u] = vec4_zero<T>();
             if (c0 + u * stride < c1)
                 a4[u] = ld_stream4_evict_first(row + c0 + u * stride);
         }
@@ -218,17 +228,17 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
             if (cc < c1)
             {
                 const float4 f = piece_f(a4[u], *reinterpret_cast<const float4*>(s.pricesf + cc));
-                if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > T)
+                if (fmaxf(fmaxf(f.x, f.y), fmaxf(f.z, f.w)) > thr)
                 {
                     const float fv[4] = {f.x, f.y, f.z, f.w};
-                    const float av[4] = {a4[u].x, a4[u].y, a4[u].z, a4[u].w};
+                    const T av[4] = {a4[u].x, a4[u].y, a4[u].z, a4[u].w};
 #pragma unroll
                     for (int e = 0; e < 4; e++)
-                        if (fv[e] > T)
+                        if (fv[e] > thr)
                         {
                             const int slot = atomicAdd(&bs.cnt, 1);
                             if (slot < kSurvCap)
-                                bs.surv[slot] = make_int2(cc + e, __float_as_int(av[e]));
+                                bs.surv[slot] = make_ent<T>(cc + e, av[e]);
                         }
                 }
             }
@@ -244,12 +254,12 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         return false;
     }
     // ---- exact values, ranks -----------------------------------------------------------------------
-    int2 mine = make_int2(0, 0);
+    CacheEnt<T> mine = make_ent<T>(0, T(0));
     double d = 0.0;
     if (tid < cnt)
     {
         mine = bs.surv[tid];
-        d = widen_exact(__int_as_float(mine.y)) - s.prices[mine.x];
+        d = widen_exact(mine.a) - s.prices[mine.col];
         bs.sval[tid] = d;
     }
     group_bar<kT>(bar_id);
@@ -259,15 +269,15 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
         for (int u = 0; u < cnt; u++)
         {
             const double y = bs.sval[u];
-            rank += (y > d) || (y == d && bs.surv[u].x < mine.x);
+            rank += (y > d) || (y == d && bs.surv[u].col < mine.col);
         }
         if (rank < kCacheK)
             s.cache[(long long)i * kCacheK + rank] = mine;
         if (rank == 0)
         {
             bs.v = d;
-            bs.j = mine.x;
-            bs.a = __int_as_float(mine.y);
+            bs.j = mine.col;
+            bs.a = mine.a;
         }
         if (rank == 1)
             bs.w = d;
@@ -275,9 +285,9 @@ __device__ __forceinline__ bool cta_scan_build(const DenseState<float>& s, Build
             bs.kth = d;
     }
     if (tid >= cnt && tid < kCacheK)
-        s.cache[(long long)i * kCacheK + tid] = make_int2(0, 0); // a == 0: not an entry
+        s.cache[(long long)i * kCacheK + tid] = make_ent<T>(0, T(0)); // a == 0: not an entry
     group_bar<kT>(bar_id);
-    const double bound_T = (double)T + (double)margin;
+    const double bound_T = (double)thr + (double)margin;
     const bool ok = bs.w > bound_T;
     if (tid == 0)
     {
@@ -296,16 +306,22 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 // chain of latencies (HBM, six barriers, two small rank loops: ~8 us when a whole CTA takes one row at
 // a time), so every CTA works on four rows at once: 256 threads and a named barrier per row, the
 // row read twice (HBM, then L2) instead of being held in registers.
-constexpr int kSweepGroupThreads = 128;
-constexpr int kSweepGroups = kThreads / kSweepGroupThreads;
-
-__device__ __noinline__ void cache_build_sweep(const DenseState<float>& s, BuildShared* bs, float margin)
+template <typename T> struct SweepGroups
 {
-    const int g = threadIdx.x / kSweepGroupThreads, gtid = threadIdx.x % kSweepGroupThreads;
-    for (int i = blockIdx.x * kSweepGroups + g; i < s.rows; i += gridDim.x * kSweepGroups)
+    // 8 rows in flight per CTA for fp32; fp64 survivors take twice the shared memory: 4 rows
+    static constexpr int threads = sizeof(T) == 4 ? 128 : 256;
+    static constexpr int count = kThreads / threads;
+};
+
+template <typename T>
+__device__ __noinline__ void cache_build_sweep(const DenseState<T>& s, BuildShared<T>* bs, float margin)
+{
+    constexpr int kGT = SweepGroups<T>::threads, kG = SweepGroups<T>::count;
+    const int g = threadIdx.x / kGT, gtid = threadIdx.x % kGT;
+    for (int i = blockIdx.x * kG + g; i < s.rows; i += gridDim.x * kG)
     {
-        cta_scan_build<kSweepGroupThreads, 0>(s, bs[g], i, margin, gtid, 1 + g);
-        group_bar<kSweepGroupThreads>(1 + g); // bs[g] is reused by the next row
+        cta_scan_build<kGT, 0, T>(s, bs[g], i, margin, gtid, 1 + g);
+        group_bar<kGT>(1 + g); // bs[g] is reused by the next row
     }
 }
 
@@ -320,13 +336,14 @@ __device__ __noinline__ void cache_build_sweep(const DenseState<float>& s, Build
 // spread and factor 7 gave the shortest solves; the landscape is noisy, +-20 % between seeds).  Rows the CTA scan cannot answer (ties) do not count; with fewer than half
 // of the samples usable the classic start of 1/4 of the coefficient range is kept.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 1) k_probe(DenseState<float> s)
+template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_probe(DenseState<T> s)
 {
-    __shared__ BuildShared bs;
+    __shared__ BuildShared<T> bs;
     const double amax = s.ctrl->amax;
     const float margin = filter_margin(amax, fmax(s.ctrl->pmax, amax));
     const int i = (int)((long long)blockIdx.x * s.rows / gridDim.x);
-    const bool ok = cta_scan_build<kThreads>(s, bs, i, margin);
+    // fp64 rows are not held in registers between the passes (they would need twice as many)
+    const bool ok = cta_scan_build<kThreads, (sizeof(T) == 4 ? BuildRegPieces<kThreads>::value : 0), T>(s, bs, i, margin);
     if (threadIdx.x == 0)
         s.ctrl->probe[blockIdx.x] = ok ? bs.v - s.cache_hdr[i].bound : -1.0;
 }

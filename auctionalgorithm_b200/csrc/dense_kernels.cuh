@@ -889,7 +889,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     const long long n_threads = (long long)gridDim.x * kThreads;
     volatile DenseCtrl* ctrl = s.ctrl;
     __shared__ NarrowShared<T> narrow_sh;
-    __shared__ BuildShared build_sh[kSweepGroups];
+    __shared__ BuildShared<T> build_sh[SweepGroups<T>::count];
 
     // The fp32 solve runs as one launch per eps phase (k_narrow finishes each phase's narrow rounds in
     // between, narrow_kernel.cuh): the loop state lives in the controller block across launches.
@@ -909,7 +909,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     double eps = ctrl->eps[phase < 0 ? 0 : phase]; // phase == -1: k_narrow restarted the schedule (escalate_schedule)
     const double amax = ctrl->amax;
     long long phase_rounds = 0; // wide rounds of the current phase in this launch
-    const bool cached = sizeof(T) == 4 && s.use_cache;
+    const bool cached = s.use_cache != 0;
     const int narrow_rows = cached ? min(s.narrow_rows, kNarrowMax) : min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
     bool handed_over = false;
 
@@ -945,23 +945,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
         {
             // narrow rounds / Gauss-Seidel tail: finishes the phase without a grid sync per round
             mode_count++;
-            if constexpr (sizeof(T) == 4)
+            if (cached && n <= narrow_rows)
             {
-                if (cached && n <= narrow_rows)
-                {
-                    // a fresh cache for every row, then this launch ends: k_narrow (one SM, prices in
-                    // shared memory) finishes the phase, the next launch starts the next one
+                // a fresh cache for every row, then this launch ends: k_narrow (one SM, prices in
+                // shared memory) finishes the phase, the next launch starts the next one
 #ifdef B200LSAP_TIMING
-                    const long long tb0 = clock64();
+                const long long tb0 = clock64();
 #endif
-                    cache_build_sweep(s, build_sh, filter_margin(amax, fmax(ctrl->pmax, amax)));
+                cache_build_sweep<T>(s, build_sh, filter_margin(amax, fmax(ctrl->pmax, amax)));
 #ifdef B200LSAP_TIMING
-                    if (tid == 0)
-                        s.ctrl->dbg[14] += clock64() - tb0;
+                if (tid == 0)
+                    s.ctrl->dbg[14] += clock64() - tb0;
 #endif
-                    handed_over = true;
-                    break;
-                }
+                handed_over = true;
+                break;
             }
             if (blockIdx.x == 0)
                 narrow_controller<T>(s, narrow_sh, s.list[cur], n, seq, mode_count, eps, amax, max_rounds - spent, ncnt);
@@ -1067,7 +1064,7 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
         for (long long i = tid; i < s.rows; i += n_threads)
             s.cache_hdr[i] = RowCacheHdr{0.0, 0, 0};
         for (long long k = tid; k < (long long)s.rows * kCacheK; k += n_threads)
-            s.cache[k] = make_int2(0, 0); // every slot always names a real column (warp_cache_eval)
+            s.cache[k] = make_ent<T>(0, T(0)); // every slot always names a real column (narrow_eval)
     }
     if (tid == 0)
     {

@@ -20,6 +20,28 @@ constexpr int kCacheK = 32;     // row cache: the best (column, a) pairs of a ro
 constexpr int kSurvCap = 256;   // most elements a CTA scan may pass on to the exact evaluation
 constexpr int kProbeRows = 128; // rows sampled to size the first eps of the scaling schedule
 
+// Row cache entry (dense_cache.cuh): a column of the row and its coefficient.  a == 0 ("no edge",
+// Auction.h:134) marks an unused slot; every slot always names a real column.
+template <typename T> struct CacheEnt;
+template <> struct __align__(8) CacheEnt<float>
+{
+    int col;
+    float a;
+};
+template <> struct __align__(16) CacheEnt<double>
+{
+    double a;
+    int col;
+    int pad;
+};
+template <typename T> __device__ __forceinline__ CacheEnt<T> make_ent(int col, T a)
+{
+    CacheEnt<T> e{};
+    e.col = col;
+    e.a = a;
+    return e;
+}
+
 // Row cache header (dense_cache.cuh): `count` valid entries in cache[row][0..count); every element of
 // the row that is NOT cached had a - p <= bound when the cache was built.  Prices never decrease,
 // so that stays true, and a bid whose second best cached value exceeds `bound` is exact.
@@ -127,9 +149,9 @@ template <typename T> struct DenseState
     int narrow_rows; // a round with at most this many bidders (and at most SMs - 1) runs as a narrow round
     int tail_rows;   // a round with at most this many bidders is finished by the Gauss-Seidel tail (0: never)
     int dry;         // 1: measurement sweep, bids are computed and stored but not offered
-    int2* cache;           // [rows][kCacheK] (column, bits of a), best first (fp32 problems only)
+    CacheEnt<T>* cache;    // [rows][kCacheK] (column, a), best first
     RowCacheHdr* cache_hdr; // [rows]
-    int use_cache;         // 1: narrow rounds answer from the row cache (fp32, persistent driver)
+    int use_cache;         // 1: narrow rounds answer from the row cache (persistent driver)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -190,12 +212,25 @@ __global__ void __launch_bounds__(256) k_absmax(const T* __restrict__ A, long lo
     const long long vec_per_row = cols4 / 4;
     const long long total = (long long)rows * vec_per_row;
     T m = T(0);
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
-         e += (long long)gridDim.x * blockDim.x)
+    const long long step = (long long)gridDim.x * blockDim.x;
+    for (long long e0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; e0 < total; e0 += 4 * step)
     {
-        const long long r = e / vec_per_row, c = (e - r * vec_per_row) * 4;
-        const V4 v = ld_stream4(A + r * ld + c);
-        m = fmax(fmax(m, fabs(v.x)), fmax(fabs(v.y), fmax(fabs(v.z), fabs(v.w))));
+        // four independent 128-bit loads in flight per thread (one at a time left the kernel at 1.5 TB/s)
+        V4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+        {
+            const long long e = e0 + u * step;
+            v[u].x = v[u].y = v[u].z = v[u].w = T(0);
+            if (e < total)
+            {
+                const long long r = e / vec_per_row, c = (e - r * vec_per_row) * 4;
+                v[u] = ld_stream4(A + r * ld + c);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            m = fmax(fmax(m, fabs(v[u].x)), fmax(fabs(v[u].y), fmax(fabs(v[u].z), fabs(v[u].w))));
     }
     double d = (double)m;
 #pragma unroll

@@ -32,10 +32,10 @@ constexpr int kNarrowThreads = 512;
 constexpr int kNarrowWarps = kNarrowThreads / 32;
 constexpr int kMissMark = -2;
 
-struct NarrowKShared
+template <typename T> struct NarrowKShared
 {
-    BuildShared bs;
-    Top2<float> part[kNarrowWarps]; // unfiltered fallback scan
+    BuildShared<T> bs;
+    Top2<T> part[kNarrowWarps]; // unfiltered fallback scan
     int q[2][kNarrowMax];           // bidders of the round / of the next round
     int col[kNarrowMax];            // column each bidder bid for (kMissMark: cache could not answer)
     int prev[kNarrowMax];           // current owner of that column
@@ -43,7 +43,7 @@ struct NarrowKShared
     int warp_count[kNarrowWarps];
     int qn, stop, nmiss, served;
     double pmax;
-    Top2<float> res; // result of the fallback scan
+    Top2<T> res; // result of the fallback scan
 };
 
 // Order-preserving map of a double to u64 (larger double <=> larger key); -0.0 is folded into +0.0
@@ -68,24 +68,24 @@ __device__ __forceinline__ double key_to_double(unsigned long long k)
 __device__ long long g_ev[8]; // developer counters of the one-bidder path
 #endif
 
-template <bool kSmem, bool kChase>
-__device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, const double* prices_s, const int* owner_s,
-                                                 const int2 e, const RowCacheHdr h, int lane, Top2<float>& t, int& prev,
+template <bool kSmem, bool kChase, typename T>
+__device__ __forceinline__ bool narrow_eval_regs(const DenseState<T>& s, const double* prices_s, const int* owner_s,
+                                                 const CacheEnt<T> e, const RowCacheHdr h, int lane, Top2<T>& t, int& prev,
                                                  long long* evp);
 
-template <bool kSmem, bool kChase = false>
-__device__ __forceinline__ bool narrow_eval(const DenseState<float>& s, const double* prices_s, const int* owner_s,
-                                            int i, int lane, Top2<float>& t, int& prev, long long* evp = nullptr)
+template <bool kSmem, bool kChase = false, typename T>
+__device__ __forceinline__ bool narrow_eval(const DenseState<T>& s, const double* prices_s, const int* owner_s,
+                                            int i, int lane, Top2<T>& t, int& prev, long long* evp = nullptr)
 {
-    return narrow_eval_regs<kSmem, kChase>(s, prices_s, owner_s, s.cache[(long long)i * kCacheK + lane], s.cache_hdr[i],
+    return narrow_eval_regs<kSmem, kChase, T>(s, prices_s, owner_s, s.cache[(long long)i * kCacheK + lane], s.cache_hdr[i],
                                            lane, t, prev, evp);
 }
 
 // The same with the row's cache entry and header already loaded (one-bidder chain: the next
 // row's loads are issued before the current bid is committed).
-template <bool kSmem, bool kChase>
-__device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, const double* prices_s, const int* owner_s,
-                                                 const int2 e, const RowCacheHdr h, int lane, Top2<float>& t, int& prev,
+template <bool kSmem, bool kChase, typename T>
+__device__ __forceinline__ bool narrow_eval_regs(const DenseState<T>& s, const double* prices_s, const int* owner_s,
+                                                 const CacheEnt<T> e, const RowCacheHdr h, int lane, Top2<T>& t, int& prev,
                                                  long long* evp)
 {
 #ifdef B200LSAP_TIMING
@@ -104,22 +104,22 @@ __device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, con
 #else
 #define EVTICK(k, ...)
 #endif
-    EVTICK(0, "r"(e.x), "r"(e.y), "r"(h.count));
-    const float a = __int_as_float(e.y);
+    EVTICK(0, "r"(e.col), "r"(h.count));
+    const T a = e.a;
     double p;
     int own;
     if (kSmem)
     {
-        p = prices_s[e.x];
-        own = owner_s[e.x];
+        p = prices_s[e.col];
+        own = owner_s[e.col];
     }
     else
     {
-        p = __ldcg(s.prices + e.x);
-        own = __ldcg(s.owner + e.x);
+        p = __ldcg(s.prices + e.col);
+        own = __ldcg(s.owner + e.col);
     }
     EVTICK(1, "d"(p), "r"(own));
-    const bool valid = a != 0.f && lane < h.count;
+    const bool valid = a != T(0) && lane < h.count;
     const unsigned long long key = valid ? ordered_key(widen_exact(a) - p) : 0ull;
     const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
     // best: max of the high words, then of the low words among those, then the lowest column
@@ -127,8 +127,8 @@ __device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, con
     const bool c1 = valid && hi == mh;
     const unsigned ml = __reduce_max_sync(kFullMask, c1 ? lo : 0u);
     const bool top = c1 && lo == ml;
-    const int mj = (int)__reduce_min_sync(kFullMask, top ? (unsigned)e.x : 0xffffffffu);
-    const bool winner = top && e.x == mj;
+    const int mj = (int)__reduce_min_sync(kFullMask, top ? (unsigned)e.col : 0xffffffffu);
+    const bool winner = top && e.col == mj;
     // second best: the same without the winner
     const unsigned hi2 = winner ? 0u : hi;
     const unsigned mh2 = __reduce_max_sync(kFullMask, hi2);
@@ -142,7 +142,7 @@ __device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, con
     t.v = key_to_double(((unsigned long long)mh << 32) | ml);
     const unsigned long long k2 = ((unsigned long long)mh2 << 32) | ml2;
     t.w = k2 ? key_to_double(k2) : -kNoSecondBest;
-    EVTICK(3, "r"(prev), "f"(t.a), "d"(t.w));
+    EVTICK(3, "r"(prev), "d"(t.w));
     // w above the -1e6 start value of the scan (Auction.h:237) and above `bound` beats every
     // column outside the cache
     return h.count >= 2 && wmask != 0 && k2 != 0 && t.w > h.bound && t.w > -kNoSecondBest;
@@ -150,14 +150,14 @@ __device__ __forceinline__ bool narrow_eval_regs(const DenseState<float>& s, con
 
 // Every thread: unfiltered scan of row i (ties, too few edges), with the -1e6 rescue of rescue_scan.
 // Result in sh.res, valid after the trailing barrier.
-__device__ __noinline__ void narrow_exact_scan(const DenseState<float>& s, NarrowKShared& sh, int i)
+template <typename T> __device__ __noinline__ void narrow_exact_scan(const DenseState<T>& s, NarrowKShared<T>& sh, int i)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const float* __restrict__ row = s.A + (long long)i * s.ld;
-    Top2<float> t = top2_empty<float>();
+    const T* __restrict__ row = s.A + (long long)i * s.ld;
+    Top2<T> t = top2_empty<T>();
     for (int c = tid * 4; c < s.cols4; c += 4 * kNarrowThreads)
     {
-        const float4 a = ld_stream4(row + c);
+        const auto a = ld_stream4(row + c);
         top2_push(t, a.x, s.prices[c], c);
         top2_push(t, a.y, s.prices[c + 1], c + 1);
         top2_push(t, a.z, s.prices[c + 2], c + 2);
@@ -169,7 +169,7 @@ __device__ __noinline__ void narrow_exact_scan(const DenseState<float>& s, Narro
     __syncthreads();
     if (warp == 0)
     {
-        Top2<float> m = lane < kNarrowWarps ? sh.part[lane] : top2_empty<float>();
+        Top2<T> m = lane < kNarrowWarps ? sh.part[lane] : top2_empty<T>();
         top2_warp_reduce(m);
         m = rescue_scan(s, i, m, lane);
         if (lane == 0)
@@ -179,8 +179,8 @@ __device__ __noinline__ void narrow_exact_scan(const DenseState<float>& s, Narro
 }
 
 // Every thread: bidders whose cache could not answer get a CTA scan (which rebuilds the cache).
-template <bool kSmem>
-__device__ __noinline__ void narrow_misses(const DenseState<float>& s, NarrowKShared& sh, const int* owner_s, const int* q,
+template <bool kSmem, typename T>
+__device__ __noinline__ void narrow_misses(const DenseState<T>& s, NarrowKShared<T>& sh, const int* owner_s, const int* q,
                                            int n, double eps, double amax)
 {
     const int tid = threadIdx.x;
@@ -191,9 +191,10 @@ __device__ __noinline__ void narrow_misses(const DenseState<float>& s, NarrowKSh
             continue;
         const int i = q[b];
         int j = -1;
-        float a = 0.f;
+        T a = T(0);
         double w = 0.0;
-        if (cta_scan_build<kNarrowThreads>(s, sh.bs, i, margin))
+        // fp64 rows are not held in registers between the passes (they would need twice as many)
+        if (cta_scan_build<kNarrowThreads, (sizeof(T) == 4 ? BuildRegPieces<kNarrowThreads>::value : 0), T>(s, sh.bs, i, margin))
         {
             j = sh.bs.j;
             a = sh.bs.a;
@@ -233,8 +234,8 @@ __device__ __noinline__ void narrow_misses(const DenseState<float>& s, NarrowKSh
 // memory nothing goes to global memory here: the same few lines would be stored to round after round
 // (a price war hits the same columns), and those stores cost the general round ~340 cycles (measured).
 // narrow_writeback publishes the state at the end of the kernel, and before any row scan.
-template <bool kSmem>
-__device__ __forceinline__ void narrow_commit(const DenseState<float>& s, double* prices_s, int* owner_s, int row, int col,
+template <bool kSmem, typename T>
+__device__ __forceinline__ void narrow_commit(const DenseState<T>& s, double* prices_s, int* owner_s, int row, int col,
                                               double bid, int prev)
 {
     if (kSmem)
@@ -254,7 +255,8 @@ __device__ __forceinline__ void narrow_commit(const DenseState<float>& s, double
 }
 
 // Every thread: global prices / pricesf / owner from the shared-memory copies (barrier included).
-__device__ __forceinline__ void narrow_flush_prices(const DenseState<float>& s, const double* prices_s, const int* owner_s)
+template <typename T>
+__device__ __forceinline__ void narrow_flush_prices(const DenseState<T>& s, const double* prices_s, const int* owner_s)
 {
     for (int j = threadIdx.x; j < s.cols; j += kNarrowThreads)
     {
@@ -267,7 +269,8 @@ __device__ __forceinline__ void narrow_flush_prices(const DenseState<float>& s, 
 }
 
 // Every thread, end of the kernel: prices, owners, and row2col rebuilt as the inverse of owner.
-__device__ __forceinline__ void narrow_writeback(const DenseState<float>& s, const double* prices_s, const int* owner_s)
+template <typename T>
+__device__ __forceinline__ void narrow_writeback(const DenseState<T>& s, const double* prices_s, const int* owner_s)
 {
     for (int i = threadIdx.x; i < s.rows; i += kNarrowThreads)
         s.row2col[i] = -1;
@@ -307,11 +310,11 @@ __device__ __forceinline__ void escalate_schedule(DenseCtrl* ctrl, int cur)
     ctrl->escalations++;
 }
 
-template <bool kSmem>
-__global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_constant__ DenseState<float> s)
+template <bool kSmem, typename T>
+__global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_constant__ DenseState<T> s)
 {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
-    __shared__ NarrowKShared sh;
+    __shared__ NarrowKShared<T> sh;
     double* const prices_s = reinterpret_cast<double*>(dyn_smem);
     int* const owner_s = reinterpret_cast<int*>(prices_s + ((s.cols + 1) & ~1));
     DenseCtrl* const ctrl = s.ctrl;
@@ -425,13 +428,13 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
 #else
                 long long* const evq = nullptr;
 #endif
-                int2 e = s.cache[(long long)i * kCacheK + lane];
+                CacheEnt<T> e = s.cache[(long long)i * kCacheK + lane];
                 RowCacheHdr h = s.cache_hdr[i];
                 for (;;)
                 {
-                    Top2<float> t;
+                    Top2<T> t;
                     int prev;
-                    if (!narrow_eval_regs<kSmem, true>(s, prices_s, owner_s, e, h, lane, t, prev, evq))
+                    if (!narrow_eval_regs<kSmem, true, T>(s, prices_s, owner_s, e, h, lane, t, prev, evq))
                         break; // the general round below scans the row
                     // the evicted row bids next: its cache is requested before this bid is committed,
                     // so the L2 latency of the load overlaps the stores
@@ -444,7 +447,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                     {
                         const double bid = (double)t.a - t.w + eps; // Auction.h:250
                         s.profits[i] = t.w - eps;                   // Auction.h:253
-                        narrow_commit<kSmem>(s, prices_s, owner_s, i, t.j, bid, prev);
+                        narrow_commit<kSmem, T>(s, prices_s, owner_s, i, t.j, bid, prev);
                         if (bid > sh.pmax)
                             sh.pmax = bid;
                     }
@@ -492,9 +495,9 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         for (int b = warp; b < n; b += kNarrowWarps)
         {
             const int i = q[b];
-            Top2<float> t;
+            Top2<T> t;
             int prev;
-            const bool hit = narrow_eval<kSmem>(s, prices_s, owner_s, i, lane, t, prev);
+            const bool hit = narrow_eval<kSmem, false, T>(s, prices_s, owner_s, i, lane, t, prev);
             if (lane == 0)
             {
                 if (hit)
@@ -519,7 +522,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         {
             if (kSmem)
                 narrow_flush_prices(s, prices_s, owner_s); // the row scans read prices from global memory
-            narrow_misses<kSmem>(s, sh, owner_s, q, n, eps, amax); // ends with a barrier
+            narrow_misses<kSmem, T>(s, sh, owner_s, q, n, eps, amax); // ends with a barrier
             if (tid == 0)
                 sh.nmiss = 0;
             if (sh.stop)
@@ -566,7 +569,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                 NTICK(7);
                 if (win)
                 {
-                    narrow_commit<kSmem>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
+                    narrow_commit<kSmem, T>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
                     if (my_bid > sh.pmax)
                         atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),
                                   (unsigned long long)__double_as_longlong(my_bid));
@@ -608,7 +611,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                         prefetch_l1(s.cache + (long long)my_prev * kCacheK + kCacheK / 2);
                         prefetch_l1(s.cache_hdr + my_prev);
                     }
-                    narrow_commit<kSmem>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
+                    narrow_commit<kSmem, T>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
                     if (my_bid > sh.pmax)
                         atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),
                                   (unsigned long long)__double_as_longlong(my_bid));

@@ -71,6 +71,23 @@ if __name__ == "__main__":
                           f"hit/miss {st['cache_hits']}/{st['cache_misses']} eps0 {st['eps_first']:.3g} restarts {st['tail_runs']}", flush=True)
                 except Exception as e:
                     print(f"{gen.__name__:16s} {str(opt):42s}: FAILED after {time.time()-t0:.1f} s: {e}", flush=True)
+    if "lsap" in which:
+        # the reference driver's own case (LSAP.cpp:23-33): 5000 x 5000 double, (Random + 1) / max
+        rng = np.random.default_rng(1)
+        a = rng.uniform(-1.0, 1.0, (5000, 5000)) + 1.0
+        a /= a.max()
+        a[a == 0.0] = 1e-12
+        for opt in (dict(), dict(row_cache=-1, eps_start=0.25), dict(eps_scaling=False)):
+            if opt.get("eps_scaling") is False and "slow" not in which:
+                continue
+            r2c, _ = h.solve(np.asfortranarray(a), want_prices=True, **opt)
+            st = h.last_stats
+            print(f"LSAP.cpp case 5000x5000 double {opt}: solve {st['ms_solve']:.2f} ms (upload {st['ms_upload']:.1f}) rounds {st['rounds']} "
+                  f"phases {st['phases']} hit/miss {st['cache_hits']}/{st['cache_misses']} objective {a[np.arange(5000), r2c].sum():.6f}", flush=True)
+        af = a.astype(np.float32)
+        r2c, _ = h.solve(np.asfortranarray(af), want_prices=True)
+        st = h.last_stats
+        print(f"same in float: solve {st['ms_solve']:.2f} ms rounds {st['rounds']} objective {af[np.arange(5000), r2c].astype(np.float64).sum():.6f}", flush=True)
     if "c4t" in which:
         dense(16384, 16384, reps=2)
     if "c4n" in which:

@@ -1,4 +1,5 @@
-// dense_cache.cuh — row caches: narrow rounds without row scans (fp32 problems).
+// dense_cache.cuh — row caches: narrow rounds without row scans (fp32 and fp64 coefficients; a cache
+// entry is (column, a): 8 bytes for float, 16 for double).
 //
 // Included by dense_kernels.cuh (needs NarrowShared, cta_bid_scan, rescue_scan).
 //

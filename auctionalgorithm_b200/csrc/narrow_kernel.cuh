@@ -1,4 +1,4 @@
-// narrow_kernel.cuh — k_narrow: the narrow rounds of an eps phase on ONE SM (fp32 problems).
+// narrow_kernel.cuh — k_narrow<kSmem, T>: the narrow rounds of an eps phase on ONE SM.
 //
 // Included by dense_kernels.cuh after dense_cache.cuh.
 //
@@ -11,8 +11,10 @@
 //     ~50-80.  Prices and owners change every round, so inside the cooperative kernel each round
 //     paid two or three L2 round trips for them;
 //   * here prices[] and owner[] live in SHARED MEMORY for the whole phase (12 bytes per column:
-//     16384 columns = 192 KB of the SM's 227 KB; global memory is written through and never read
-//     back), which the cooperative kernel cannot afford: its sweeps need that space as L1;
+//     16384 columns = 192 KB of the SM's 227 KB; kSmem, chosen by the host when they fit).  Global
+//     memory is not touched per round: prices are flushed before any row scan (narrow_flush_prices)
+//     and everything is written back once at the end (narrow_writeback rebuilds row2col from
+//     owner).  The cooperative kernel cannot afford this: its sweeps need that space as L1;
 //   * 512 threads at up to 128 registers instead of 1024 at 64: the round loop holds its state in
 //     registers (at 64 every loop-carried value was spilled, and a spill store per round turns the
 //     reloads from that stack line into L2 round trips);

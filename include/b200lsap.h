@@ -62,9 +62,11 @@ typedef struct
 {
     double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
     int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on */
-    double eps_start;      /* first eps of the scaling schedule; <= 0: default (fp32: an eighth of the mean
-                              spread of a row's best ~36 values, measured on sampled rows, at most 0.25;
-                              fp64: 0.25).  Only the LAST phase, at eps_multiplier / cols, decides the result. */
+    double eps_start;      /* first eps of the scaling schedule; <= 0: default (an eighth of the mean spread
+                              of a row's best ~36 values, measured on 128 sampled rows, at most 0.25).
+                              A default first phase that runs over its work budget
+                              restarts from a larger eps (stats.tail_runs).  Only the LAST phase, at
+                              eps_multiplier / cols, decides the result. */
     double eps_factor;     /* eps is divided by this between phases; <= 1: default (7) */
     int64_t max_rounds;    /* watchdog; <= 0: default */
     int32_t driver;        /* 0 persistent cooperative kernel (default); 1 one launch per phase
@@ -76,7 +78,7 @@ typedef struct
                               narrow round: one CTA per bidder row, a controller CTA instead of grid
                               syncs; 0: default (SMs - 1), -1: never.  Persistent driver only. */
     int32_t row_cache;     /* narrow rounds answer from per-row caches of the best columns instead of
-                              scanning rows (fp32, persistent driver; bit-identical bids): 0 default (on),
+                              scanning rows (persistent driver; bit-identical bids): 0 default (on),
                               -1 off */
 } b200lsap_options;
 
@@ -91,10 +93,10 @@ typedef struct
     double ms_solve;   /* auction kernels only, CUDA events on the handle's stream */
     double ms_download;
     int64_t launches;  /* kernels launched by this call */
-    int64_t tail_bids; /* fp32 with row caches: bids of one-bidder rounds (k_narrow's single-warp chain; included
+    int64_t tail_bids; /* with row caches: bids of one-bidder rounds (k_narrow's single-warp chain; included
                           in bids and in rounds).  Row-scanning paths: bids placed by the Gauss-Seidel tail
                           (included in bids, not in rounds) */
-    int64_t tail_runs; /* row-scanning paths: times the tail took over.  fp32 with row caches: times the
+    int64_t tail_runs; /* row-scanning paths: times the tail took over.  With row caches: times the
                           data-sized schedule was restarted from a larger eps (first phase over budget) */
     int64_t narrow_rounds; /* rounds run as narrow rounds (included in rounds) */
     int64_t cache_hits;    /* narrow-round bids answered from the row cache alone */

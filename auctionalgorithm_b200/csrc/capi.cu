@@ -61,7 +61,10 @@ struct b200lsap_handle
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t last_cols = 0; // prices of the last dense solve are valid for this many columns
+    const void* last_a = nullptr; // matrix of that solve when it was used in place (candidate lists stay valid)
+    int64_t last_rows = 0, last_ld = 0;
     int min_seg = 512;
+    int sweep_split = 0;
     int max_parts = 4;
     int64_t launches = 0;
     double eps_probe_scale = 0.125; // developer knob B200LSAP_EPS_SCALE
@@ -187,6 +190,8 @@ int b200lsap_create(b200lsap_handle** out, int device)
         if (v > 0)
             h->eps_probe_scale = v;
     }
+    if (const char* s = getenv("B200LSAP_SWEEP_SPLIT"))
+        h->sweep_split = std::max(0, atoi(s));
     if (const char* s = getenv("B200LSAP_MIN_SEG"))
     {
         int v = atoi(s);
@@ -333,7 +338,7 @@ template <typename T> int alloc_state(b200lsap_handle* h, int64_t rows, int64_t 
     CU(h->bid_val.ensure(rows * sizeof(double)));
     CU(h->list0.ensure(rows * sizeof(int)));
     CU(h->list1.ensure(rows * sizeof(int)));
-    CU(h->partial.ensure((size_t)(total_warps + 64) * sizeof(Top2<T>)));
+    CU(h->partial.ensure((size_t)std::max<int64_t>(total_warps + 64, 4 * rows) * sizeof(Top2<T>)));
     CU(h->arrive.ensure(rows * sizeof(int)));
     CU(h->ctrl.ensure(sizeof(DenseCtrl)));
     return B200LSAP_OK;
@@ -368,6 +373,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.arrive = h->arrive.as<int>();
     s.ctrl = h->ctrl.as<DenseCtrl>();
     s.min_seg = h->min_seg;
+    s.sweep_split = h->sweep_split;
     s.tail_rows = 0;
     s.dry = 0;
     return s;
@@ -544,6 +550,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     }
     CU(cudaGetLastError());
     h->last_cols = plan.cols;
+    h->last_a = nullptr;
     if (stats)
     {
         float ms = 0.f;
@@ -703,6 +710,8 @@ int solve_device(b200lsap_handle* h, const T* a, int64_t rows, int64_t cols, int
     rc = run_dense<T>(h, A, ldA, plan, stats);
     if (rc)
         return rc;
+    if ((const void*)A == (const void*)a) // used in place: the candidate lists describe the caller's matrix
+        h->last_a = a, h->last_rows = rows, h->last_ld = ld;
     CU(cudaMemcpyAsync(row_to_col_dev, h->row2col.p, rows * sizeof(int32_t), cudaMemcpyDeviceToDevice, h->stream));
     if (prices_dev)
         CU(cudaMemcpyAsync(prices_dev, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
@@ -980,12 +989,13 @@ int b200lsap_bid_sweep_device_f32(b200lsap_handle* h, const float* a_dev, int64_
     if (rc)
         return rc;
     const bool keep = use_last_prices && h->last_cols == cols;
+    const bool keep_cand = keep && h->last_a == (const void*)a_dev && h->last_rows == rows && h->last_ld == ld;
     rc = alloc_state<float>(h, rows, cols, ld, grid * kWarpsPerBlock);
     if (rc)
         return rc;
     DenseState<float> s = bind_state<float>(h, a_dev, rows, cols, ld);
     s.dry = 1;
-    k_init<float><<<grid, kThreads, 0, h->stream>>>(s, keep ? 1 : 0);
+    k_init<float><<<grid, kThreads, 0, h->stream>>>(s, keep_cand ? 2 : keep ? 1 : 0);
     k_absmax<float><<<grid_for(h, rows * (int64_t)(s.cols4 / 4), 256 * 8), 256, 0, h->stream>>>(s.A, s.ld, s.rows, s.cols4,
                                                                                         s.ctrl);
     CU(cudaEventRecord(h->ev[1], h->stream));

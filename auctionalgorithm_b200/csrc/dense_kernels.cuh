@@ -119,7 +119,7 @@ template <bool kDeep> struct FilterScan
     __device__ __forceinline__ explicit FilterScan(float thr0) : t(top2_empty<float, kDeep>()), thr(thr0) {}
 };
 
-constexpr int kScanU = 4;
+constexpr int kScanU = 4; // 16-byte loads in flight per lane; 8 is slower (read_probe.cu shows the same for plain reads)
 
 // warp-wide top-2 of per-lane (hi >= lo) pairs of floats; every lane ends with the result
 __device__ __forceinline__ void warp_top2f(float& hi, float& lo)
@@ -134,22 +134,26 @@ __device__ __forceinline__ void warp_top2f(float& hi, float& lo)
     }
 }
 
-template <bool kDeep>
-__device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* __restrict__ row,
-                                           const double* prices, const float* pricesf, float margin, int first,
-                                           int stride, int c1)
+// the U pieces of one batch, in flight together
+__device__ __forceinline__ void scan_load(float4 (&a)[kScanU], const float* __restrict__ row, int first, int stride,
+                                          int c1)
 {
-    constexpr int U = kScanU;
-    float4 a[U];
-    float m = -INFINITY;
 #pragma unroll
-    for (int u = 0; u < U; u++)
+    for (int u = 0; u < kScanU; u++)
     {
         const int cc = first + u * stride;
         a[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (cc < c1)
             a[u] = ld_stream4(row + cc);
     }
+}
+
+template <bool kDeep>
+__device__ __forceinline__ void scan_consume(FilterScan<kDeep>& st, const float4 (&a)[kScanU], const double* prices,
+                                             const float* pricesf, float margin, int first, int stride, int c1)
+{
+    constexpr int U = kScanU;
+    float m = -INFINITY;
 #pragma unroll
     for (int u = 0; u < U; u++)
     {
@@ -210,6 +214,16 @@ __device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* _
                 top2_push(st.t, a[u].w, prices[cc + 3], cc + 3);
         }
     }
+}
+
+template <bool kDeep>
+__device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* __restrict__ row,
+                                           const double* prices, const float* pricesf, float margin, int first,
+                                           int stride, int c1)
+{
+    float4 a[kScanU];
+    scan_load(a, row, first, stride, c1);
+    scan_consume(st, a, prices, pricesf, margin, first, stride, c1);
 }
 
 // Warp-uniform starting threshold of row i from its candidate list (kCand (column, a) pairs left
@@ -350,11 +364,96 @@ template <typename T> __device__ __forceinline__ void cand_store(const DenseStat
         __stcg(s.cand + (long long)i * kCand + slot, make_int2(j, __float_as_int(a)));
 }
 
+// ---------------------------------------------------------------------------------------------
+// Wide sweeps in half rows.  With more bidders than warps a warp takes whole rows one after the
+// other, and the last wave of rows leaves part of the machine idle: 16384 rows on 4736 warps are
+// 3.46 rows per warp, the warps with four rows finish alone (a read-only probe of the same access
+// pattern loses 11 % to this, tools/micro/read_probe.cu).  Here the two warps 2k, 2k+1 of a CTA
+// take the two halves of the same row (6.92 rows per pair: 7 waves, 98.8 % full) and merge their
+// top-2 through shared memory: an mbarrier per pair (two arrivals), results double buffered so that
+// the next row's result never overwrites one that is still being read.  No global memory, fences or
+// atomics, which the general split-row path below needs.
+// sweep_split 0: when whole rows would leave the last wave under 95 % full and half rows do
+// better; 1: never; 2: whenever there are at least as many bidders as warps.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool pair_rounds(int n, int total_warps, int cols4, int min_seg, int sweep_split)
+{
+    if (n < total_warps || sweep_split == 1 || cols4 / 2 < min_seg || (total_warps & 1))
+        return false;
+    if (sweep_split >= 2)
+        return true;
+    const long long w1 = (n + total_warps - 1) / total_warps, w2 = (2ll * n + total_warps - 1) / total_warps;
+    return 100ll * n < 95ll * w1 * total_warps && w2 < 2 * w1;
+}
+
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+template <typename T> struct PairShared
+{
+    unsigned long long bar[kWarpsPerBlock / 2];
+    Top2<T> res[kWarpsPerBlock / 2][2];
+};
+
+template <typename T>
+__device__ __forceinline__ void bid_phase_pairs(const DenseState<T>& s, const int* __restrict__ list, int n, double eps,
+                                                float margin, double pmax, int warp_global, int total_warps, int lane)
+{
+    __shared__ PairShared<T> ps;
+    const int wp = (threadIdx.x >> 5) >> 1, half = (threadIdx.x >> 5) & 1;
+    __syncthreads();
+    if (threadIdx.x < kWarpsPerBlock / 2)
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 2;" ::"r"(smem_addr(&ps.bar[threadIdx.x])));
+    __syncthreads();
+    int seg = (s.cols4 + 1) / 2;
+    seg = (seg + 127) & ~127;
+    const int c0 = half * seg, c1 = min(c0 + seg, s.cols4);
+    const unsigned bar = smem_addr(&ps.bar[wp]);
+    unsigned k = 0;
+    for (int b = warp_global >> 1; b < n; b += total_warps >> 1, k++)
+    {
+        const int i = list[b];
+        const float thr0 = cand_threshold(s, i, margin, lane);
+        Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, thr0, c0, c1, lane);
+        if (t.j >= 0)
+            cand_store(s, i, (t.j >> 2) & (kCand - 1), t.j, t.a);
+        top2_warp_reduce_sparse(t);
+        if (half == 1 && lane == 0)
+            ps.res[wp][k & 1] = t;
+        __syncwarp();
+        if (lane == 0)
+            asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        unsigned ok;
+        do
+        {
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                         : "=r"(ok)
+                         : "r"(bar), "r"(k & 1)
+                         : "memory");
+        } while (!ok);
+        if (half == 0)
+        {
+            const Top2<T> o = ps.res[wp][k & 1];
+            top2_merge(t, o);
+            t = rescue_scan(s, i, t, lane);
+            if (lane == 0)
+                submit_bid(s, i, t, eps, pmax);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < kWarpsPerBlock / 2)
+        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_addr(&ps.bar[threadIdx.x])));
+}
+
 template <typename T>
 __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __restrict__ list, int n, double eps,
                                           double amax, double pmax, int warp_global, int total_warps, int lane)
 {
     const float margin = filter_margin(amax, pmax);
+    if (pair_rounds(n, total_warps, s.cols4, s.min_seg, s.sweep_split))
+    {
+        bid_phase_pairs<T>(s, list, n, eps, margin, pmax, warp_global, total_warps, lane);
+        return;
+    }
     const int S = split_factor(n, total_warps, s.cols4, s.min_seg);
     int seg = (s.cols4 + S - 1) / S;
     seg = (seg + 127) & ~127; // segments start on 512-byte boundaries
@@ -365,9 +464,11 @@ __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __r
         const int i = list[b];
         const int c0 = sg * seg;
         const int c1 = min(c0 + seg, s.cols4);
-        // a whole row per warp tightens its own threshold after the first of many batches; the
-        // candidate list (one more dependent L2 access) pays only for short segments
-        const float thr0 = S == 1 ? -INFINITY : cand_threshold(s, i, margin, lane);
+        // Without a starting threshold a scan takes the exact path in its first batch and again at
+        // every batch that beats its running second best (about 2 ln(batches) times: 7 of a whole
+        // row's 32 batches); with the candidates' threshold only the batches that hold the row's
+        // best columns do.  Measured on 16384 x 16384: 5.2 -> 6.0 TB/s for whole rows.
+        const float thr0 = cand_threshold(s, i, margin, lane);
         Top2<T> t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, thr0, c0, c1, lane);
         if (S == 1)
         {
@@ -1057,8 +1158,9 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init(Dens
     }
     for (long long j = tid; j < s.cols; j += n_threads)
         s.slots[j] = BidSlot{0ull, 0ull};
-    for (long long k = tid; k < (long long)s.rows * kCand; k += n_threads)
-        s.cand[k] = make_int2(-1, 0);
+    if (keep_prices < 2) // 2: same matrix as before; candidates are edges of their rows whatever the prices
+        for (long long k = tid; k < (long long)s.rows * kCand; k += n_threads)
+            s.cand[k] = make_int2(-1, 0);
     if (s.cache_hdr)
     {
         for (long long i = tid; i < s.rows; i += n_threads)

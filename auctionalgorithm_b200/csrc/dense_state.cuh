@@ -139,10 +139,11 @@ template <typename T> struct DenseState
     int* bid_col;    // [rows] column the row bid for this round
     double* bid_val; // [rows] its bid
     int* list[2];    // compacted unassigned rows, double buffered
-    Top2<T>* partial; // [capacity >= total warps] split-row partial results
+    Top2<T>* partial; // [capacity >= max(total warps, 4 rows)] split-row partial results
     int* arrive;     // [rows] split-row arrival counters (zero between rounds)
     DenseCtrl* ctrl;
     int min_seg;     // smallest row segment a warp takes when rows are split (multiple of 128)
+    int sweep_split; // rounds with more bidders than warps: 0 balance the last wave, 1 whole rows, >= 2 parts per row
     int2* cand;      // [rows][kCand] (column, bits of a): edges that were among the row's best, -1: empty
     NarrowCtrl* narrow;
     int max_parts;   // narrow rounds: at most this many CTAs share one bidder's row (power of two)

@@ -190,9 +190,13 @@ int b200lsap_shard_next_phase(b200lsap_handle* handle, int* more);
 int b200lsap_shard_finish(b200lsap_handle* handle, int32_t* row_to_col_dev, double* prices_dev,
                           b200lsap_stats* stats);
 
-/* Full-sweep bidding pass for measurement: every row bids once against the handle's current
- * prices of the last device solve (or zero prices), nothing is updated.  Returns through
- * ms_out the CUDA-event time of that single kernel; bytes_out = rows*cols*sizeof(float). */
+/* Full-sweep bidding pass for measurement: every row bids once, nothing is updated.
+ * use_last_prices = 0: the state a solve starts from (zero prices, no candidate lists: the first
+ * sweep of the first eps phase).  1: the state the handle's last dense solve left: its prices and,
+ * when that solve ran in place on this very device matrix (same pointer, shape and ld; the
+ * caller has not changed it), the rows' candidate lists, i.e. what the first sweep of every
+ * later eps phase starts from.  Returns through ms_out the CUDA-event time of that single
+ * kernel; bytes_out = rows*cols*sizeof(float). */
 int b200lsap_bid_sweep_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols,
                                   int64_t ld, int use_last_prices, double* ms_out, int64_t* bytes_out);
 

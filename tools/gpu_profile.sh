@@ -3,8 +3,8 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
 TAG=${1:-r1e}
-timeout 300 python tools/quick_bench.py sweep > gpurun_out/sweep_plain.log 2>&1 && \
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_bid -s 1 -c 1 -f -o gpurun_out/${TAG}_kbid python tools/quick_bench.py sweep > gpurun_out/ncu_kbid.log 2>&1
+timeout 300 python tools/quick_bench.py sweep2 > gpurun_out/sweep_plain.log 2>&1 && \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_bid -s 12 -c 1 -f -o gpurun_out/${TAG}_kbid python tools/quick_bench.py sweep2 > gpurun_out/ncu_kbid.log 2>&1
 timeout 300 python tools/quick_bench.py c3s > gpurun_out/c3_plain.log 2>&1 && \
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_auction_batch -s 1 -c 1 -f -o gpurun_out/${TAG}_batch python tools/quick_bench.py c3s > gpurun_out/ncu_batch.log 2>&1
 timeout 300 python tools/quick_bench.py c4t > gpurun_out/c4_plain.log 2>&1 && \

@@ -47,6 +47,17 @@ if __name__ == "__main__":
         for _ in range(4):
             ms, nb = h.bid_sweep_device(t.data_ptr(), 16384, 16384, 16384, False)
             print(f"sweep 16384^2: {ms:.4f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
+    if "sweep2" in which:  # zero prices and the prices a solve leaves; min of 8 launches each
+        t = torch.empty((16384, 16384), dtype=torch.float32, device="cuda")
+        h.generate_device(t.data_ptr(), 1, 16384, 16384, 16384, 1, 1)
+        a = [h.bid_sweep_device(t.data_ptr(), 16384, 16384, 16384, False)[0] for _ in range(8)]
+        r2c = torch.empty(16384, dtype=torch.int32, device="cuda")
+        st = h.solve_device(t.data_ptr(), 16384, 16384, 16384, 1, r2c.data_ptr())
+        st = h.solve_device(t.data_ptr(), 16384, 16384, 16384, 1, r2c.data_ptr())
+        b = [h.bid_sweep_device(t.data_ptr(), 16384, 16384, 16384, True)[0] for _ in range(8)]
+        nb = 16384 * 16384 * 4
+        print(f"sweep2: zero prices min {min(a):.4f} mean {sum(a[3:])/5:.4f} ms -> {nb/min(a)/1e6:.0f} GB/s | last prices min {min(b):.4f} "
+              f"mean {sum(b[3:])/5:.4f} ms -> {nb/(sum(b[3:])/5)/1e6:.0f} GB/s | solve {st['ms_solve']:.2f} ms", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
     if "c4f" in which:

@@ -47,6 +47,12 @@ SIGNATURES = {
                                             C.POINTER(Stats)]),
     "b200lsap_solve_device_f64": (C.c_int, [_H, _P, _i64, _i64, _i64, C.c_int, C.POINTER(Options), _P, _P,
                                             C.POINTER(Stats)]),
+    "b200lsap_solve_csr_f32": (C.c_int, [_H, _P, _P, _P, _i64, _i64, _i64, C.POINTER(Options), _P, _P, C.POINTER(Stats)]),
+    "b200lsap_solve_csr_f64": (C.c_int, [_H, _P, _P, _P, _i64, _i64, _i64, C.POINTER(Options), _P, _P, C.POINTER(Stats)]),
+    "b200lsap_solve_csr_device_f32": (C.c_int, [_H, _P, _P, _P, _i64, _i64, _i64, C.POINTER(Options), _P, _P,
+                                                C.POINTER(Stats)]),
+    "b200lsap_solve_csr_device_f64": (C.c_int, [_H, _P, _P, _P, _i64, _i64, _i64, C.POINTER(Options), _P, _P,
+                                                C.POINTER(Stats)]),
     "b200lsap_solve_batch_f32": (C.c_int, [_H, _P, _i64, C.c_int32, C.c_int32, C.c_int, C.POINTER(Options), _P,
                                            C.POINTER(Stats)]),
     "b200lsap_solve_batch_device_f32": (C.c_int, [_H, _P, _i64, C.c_int32, C.c_int32, C.c_int, C.POINTER(Options), _P,

@@ -13,6 +13,7 @@
 #include "batch_kernels.cuh"
 #include "dense_kernels.cuh"
 #include "shard_kernels.cuh"
+#include "sparse_kernels.cuh"
 
 using namespace b200lsap;
 
@@ -56,7 +57,7 @@ struct b200lsap_handle
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     std::string err;
-    DevBuf a, staging, prices, pricesf, cand, cache, cache_hdr, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
+    DevBuf a, staging, csr_ptr, csr_col, csr_val, prices, pricesf, cand, cache, cache_hdr, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
         ctrl, out64, batch_in, batch_out;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -208,7 +209,7 @@ int b200lsap_destroy(b200lsap_handle* h)
         return B200LSAP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    for (DevBuf* b : {&h->a, &h->staging, &h->prices, &h->pricesf, &h->cand, &h->narrow, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
+    for (DevBuf* b : {&h->a, &h->staging, &h->csr_ptr, &h->csr_col, &h->csr_val, &h->prices, &h->pricesf, &h->cand, &h->cache, &h->cache_hdr, &h->narrow, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
                       &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
                       &h->batch_out})
         b->release();
@@ -755,6 +756,195 @@ int b200lsap_solve_device_f64(b200lsap_handle* h, const double* a, int64_t rows,
                               const b200lsap_options* opts, int32_t* r2c, double* prices, b200lsap_stats* stats)
 {
     return solve_device<double>(h, a, rows, cols, ld, layout, opts, r2c, prices, stats);
+}
+
+} // extern "C"
+
+// =============================================================================================
+// Sparse row-major (CSR) solve: Auction<Scalar, Eigen::SparseMatrix<Scalar, Eigen::RowMajor>>::solve
+// =============================================================================================
+namespace
+{
+
+// start of a CSR solve: the part of k_init the sparse kernels need (no candidate lists, no row caches)
+template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init_csr(DenseState<T> s)
+{
+    const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+    const long long n_threads = (long long)gridDim.x * kThreads;
+    reset_phase(s, s.list[0], tid, n_threads);
+    for (long long i = tid; i < s.rows; i += n_threads)
+        s.profits[i] = 1.0; // Auction.h:58
+    for (long long j = tid; j < s.cols; j += n_threads)
+    {
+        s.prices[j] = 0.0;
+        s.pricesf[j] = 0.f;
+        s.slots[j] = BidSlot{0ull, 0ull};
+    }
+}
+
+template <typename T>
+int solve_csr(b200lsap_handle* h, const T* values, const int32_t* row_ptr, const int32_t* col_idx, int64_t rows,
+              int64_t cols, int64_t nnz, bool on_host, const b200lsap_options* opts, void* row_to_col, double* prices_out,
+              b200lsap_stats* stats)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (!values || !row_ptr || !col_idx || !row_to_col)
+        return fail(h, B200LSAP_ERR_ARG, "null argument");
+    if (rows < 1 || cols < 1 || rows > cols || cols > 0x7fff0000ll || nnz < rows || nnz > 0x7fff0000ll)
+        return fail(h, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    if (on_host)
+    {
+        // the reference never returns on these
+        if (row_ptr[0] != 0 || row_ptr[rows] != nnz)
+            return fail(h, B200LSAP_ERR_ARG, "row_ptr[0] must be 0 and row_ptr[rows] must equal nnz");
+        for (int64_t i = 0; i < rows; i++)
+            if (row_ptr[i + 1] <= row_ptr[i])
+                return fail(h, row_ptr[i + 1] < row_ptr[i] ? B200LSAP_ERR_ARG : B200LSAP_ERR_INFEASIBLE,
+                            row_ptr[i + 1] < row_ptr[i] ? "row_ptr is not monotone" : "a row without a stored entry");
+    }
+    CU(cudaSetDevice(h->device));
+    DensePlan plan;
+    int rc = make_plan(h, rows, cols, opts, plan);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    h->launches = 0;
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    CsrView<T> m;
+    m.nnz = nnz;
+    if (on_host)
+    {
+        CU(h->csr_ptr.ensure((rows + 1) * sizeof(int32_t)));
+        CU(h->csr_col.ensure(nnz * sizeof(int32_t)));
+        CU(h->csr_val.ensure(nnz * sizeof(T)));
+        CU(cudaMemcpyAsync(h->csr_ptr.p, row_ptr, (rows + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->csr_col.p, col_idx, nnz * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->csr_val.p, values, nnz * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+        m.ptr = h->csr_ptr.as<int>();
+        m.col = h->csr_col.as<int>();
+        m.val = h->csr_val.as<T>();
+    }
+    else
+    {
+        m.ptr = row_ptr;
+        m.col = col_idx;
+        m.val = values;
+    }
+    // the arrays of a round (prices, owners, bid slots, bidder lists); no candidate lists or row caches
+    CU(h->prices.ensure((cols + 512) * sizeof(double)));
+    CU(h->pricesf.ensure((cols + 512) * sizeof(float)));
+    CU(h->profits.ensure(rows * sizeof(double)));
+    CU(h->slots.ensure(cols * sizeof(BidSlot)));
+    CU(h->owner.ensure(cols * sizeof(int)));
+    CU(h->row2col.ensure(rows * sizeof(int)));
+    CU(h->bid_col.ensure(rows * sizeof(int)));
+    CU(h->bid_val.ensure(rows * sizeof(double)));
+    CU(h->list0.ensure(rows * sizeof(int)));
+    CU(h->list1.ensure(rows * sizeof(int)));
+    CU(h->ctrl.ensure(sizeof(DenseCtrl)));
+    DenseState<T> s = bind_state<T>(h, (const T*)nullptr, rows, cols, cols);
+    DenseCtrl* hc = h->h_ctrl;
+    memset(hc, 0, sizeof *hc);
+    hc->count[0] = (int)rows;
+    hc->n_phases = (int)plan.eps.size();
+    hc->max_rounds = plan.max_rounds;
+    for (size_t k = 0; k < plan.eps.size(); k++)
+        hc->eps[k] = plan.eps[k];
+    CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_auction_csr<T>, kThreads, 0));
+    if (per_sm < 1)
+        return fail(h, B200LSAP_ERR_CUDA, "sparse kernel does not fit on an SM");
+    // no more CTAs than the first round has warps of work for
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(h->num_sms, (rows + kWarpsPerBlock - 1) / kWarpsPerBlock));
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_init_csr<T><<<grid, kThreads, 0, h->stream>>>(s);
+    k_absmax_csr<T><<<grid_for(h, nnz, 256 * 8), 256, 0, h->stream>>>(m.val, nnz, s.ctrl);
+    void* args[] = {&s, &m};
+    CU(cudaLaunchCooperativeKernel((void*)k_auction_csr<T>, dim3(grid), dim3(kThreads), args, 0, h->stream));
+    h->launches += 3;
+    CU(cudaMemcpyAsync(hc, s.ctrl, sizeof *hc, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    h->last_cols = 0;
+    h->last_a = nullptr;
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+        stats->ms_solve = ms;
+        stats->rounds = hc->rounds;
+        stats->bids = hc->bids;
+        stats->phases = hc->phase + 1;
+        stats->narrow_rounds = hc->narrow_rounds;
+        stats->bid_bytes = hc->bids * (nnz / rows) * (int64_t)(sizeof(T) + sizeof(int32_t)); // average row
+        stats->eps_final = plan.eps.back();
+        stats->eps_first = plan.eps.front();
+    }
+    if (hc->status != 0)
+        return fail(h, hc->status, b200lsap_status_string(hc->status));
+    if (on_host)
+    {
+        CU(h->out64.ensure(rows * sizeof(long long)));
+        k_widen_i32<<<grid_for(h, rows, 256), 256, 0, h->stream>>>(h->row2col.as<int>(), h->out64.as<long long>(), rows);
+        h->launches++;
+        CU(cudaMemcpyAsync(row_to_col, h->out64.p, rows * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+        if (prices_out)
+            CU(cudaMemcpyAsync(prices_out, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    else
+    {
+        CU(cudaMemcpyAsync(row_to_col, h->row2col.p, rows * sizeof(int32_t), cudaMemcpyDeviceToDevice, h->stream));
+        if (prices_out)
+            CU(cudaMemcpyAsync(prices_out, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    }
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]);
+        stats->ms_upload = ms;
+        cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
+        stats->ms_download = ms;
+        stats->launches = h->launches;
+    }
+    return B200LSAP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int b200lsap_solve_csr_f32(b200lsap_handle* h, const float* values, const int32_t* row_ptr, const int32_t* col_idx,
+                           int64_t rows, int64_t cols, int64_t nnz, const b200lsap_options* opts, int64_t* row_to_col,
+                           double* prices_out, b200lsap_stats* stats)
+{
+    return solve_csr<float>(h, values, row_ptr, col_idx, rows, cols, nnz, true, opts, row_to_col, prices_out, stats);
+}
+
+int b200lsap_solve_csr_f64(b200lsap_handle* h, const double* values, const int32_t* row_ptr, const int32_t* col_idx,
+                           int64_t rows, int64_t cols, int64_t nnz, const b200lsap_options* opts, int64_t* row_to_col,
+                           double* prices_out, b200lsap_stats* stats)
+{
+    return solve_csr<double>(h, values, row_ptr, col_idx, rows, cols, nnz, true, opts, row_to_col, prices_out, stats);
+}
+
+int b200lsap_solve_csr_device_f32(b200lsap_handle* h, const float* values, const int32_t* row_ptr, const int32_t* col_idx,
+                                  int64_t rows, int64_t cols, int64_t nnz, const b200lsap_options* opts,
+                                  int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    return solve_csr<float>(h, values, row_ptr, col_idx, rows, cols, nnz, false, opts, row_to_col_dev, prices_dev, stats);
+}
+
+int b200lsap_solve_csr_device_f64(b200lsap_handle* h, const double* values, const int32_t* row_ptr, const int32_t* col_idx,
+                                  int64_t rows, int64_t cols, int64_t nnz, const b200lsap_options* opts,
+                                  int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    return solve_csr<double>(h, values, row_ptr, col_idx, rows, cols, nnz, false, opts, row_to_col_dev, prices_dev, stats);
 }
 
 } // extern "C"

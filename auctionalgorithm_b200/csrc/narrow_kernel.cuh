@@ -644,10 +644,10 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         NTICK(6);
 #ifdef B200LSAP_TIMING
         {
-            // whole general round by number of bidders: 1-4, 5-8, 9-32, 33-256
+            // whole general round by number of bidders: 1-4, 5-16, 17-32, 33-256
             const long long dt = clock64() - t_round;
             if (n <= 4) { bk_c0 += dt; bk_r0++; }
-            else if (n <= 8) { bk_c1 += dt; bk_r1++; }
+            else if (n <= 16) { bk_c1 += dt; bk_r1++; }
             else if (n <= 32) { bk_c2 += dt; bk_r2++; }
             else { bk_c3 += dt; bk_r3++; }
         }
@@ -682,6 +682,12 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->dbg[8] += rounds;
         ctrl->dbg[9] += bids;
         ctrl->dbg[1] += fast;
+#if B200LSAP_VAR == 12 // rounds and cycles of the general rounds by number of bidders
+        ctrl->dbg[2] += bk_r0; ctrl->dbg[3] += bk_c0;
+        ctrl->dbg[4] += bk_r1; ctrl->dbg[5] += bk_c1;
+        ctrl->dbg[6] += bk_r2; ctrl->dbg[7] += bk_c2;
+        ctrl->dbg[10] += bk_r3; ctrl->dbg[11] += bk_c3;
+#else
         ctrl->dbg[2] += acc2;
         ctrl->dbg[3] += acc3;
         ctrl->dbg[4] += acc4;
@@ -689,6 +695,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->dbg[6] += acc6;
         ctrl->dbg[7] += acc7;
         ctrl->dbg[10] += bk_r0; ctrl->dbg[11] += bk_c0;
+#endif
 #endif
     }
 }

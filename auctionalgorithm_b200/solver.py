@@ -124,6 +124,40 @@ class Handle:
         self._check(rc)
         return self.last_stats
 
+    def solve_csr(self, values: np.ndarray, row_ptr: np.ndarray, col_idx: np.ndarray, rows: int, cols: int,
+                  want_prices: bool = False, **options):
+        """Compressed row-major sparse matrix in (Eigen's valuePtr / outerIndexPtr / innerIndexPtr, scipy's
+        csr data / indptr / indices with sorted indices), row_to_col (int64[rows]) out: the reference's
+        Auction<Scalar, SparseMatrix<Scalar, RowMajor>>::solve (Auction.h:166-198)."""
+        values = np.ascontiguousarray(values)
+        if values.dtype not in (np.float32, np.float64):
+            raise TypeError("use real types as coefficients (Auction.h:40): float32 or float64")
+        row_ptr = np.ascontiguousarray(row_ptr, np.int32)
+        col_idx = np.ascontiguousarray(col_idx, np.int32)
+        if row_ptr.shape[0] != rows + 1 or col_idx.shape[0] != values.shape[0]:
+            raise ValueError("row_ptr needs rows + 1 entries and col_idx one per value")
+        r2c = np.full(max(rows, 1), -1, np.int64)
+        prices = np.zeros(max(cols, 1), np.float64) if want_prices else None
+        st = Stats()
+        o = self._opts(**options)
+        fn = self._lib.b200lsap_solve_csr_f32 if values.dtype == np.float32 else self._lib.b200lsap_solve_csr_f64
+        rc = fn(self._h, values.ctypes.data, row_ptr.ctypes.data, col_idx.ctypes.data, rows, cols, values.shape[0],
+                C.byref(o), r2c.ctypes.data, prices.ctypes.data if want_prices else None, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return (r2c[:rows], prices) if want_prices else r2c[:rows]
+
+    def solve_csr_device(self, values_ptr: int, row_ptr_ptr: int, col_idx_ptr: int, rows: int, cols: int, nnz: int,
+                         r2c_ptr: int, prices_ptr: int = 0, dtype=np.float32, **options) -> dict:
+        st = Stats()
+        o = self._opts(**options)
+        fn = self._lib.b200lsap_solve_csr_device_f32 if dtype == np.float32 else self._lib.b200lsap_solve_csr_device_f64
+        rc = fn(self._h, C.c_void_p(values_ptr), C.c_void_p(row_ptr_ptr), C.c_void_p(col_idx_ptr), rows, cols, nnz,
+                C.byref(o), C.c_void_p(r2c_ptr), C.c_void_p(prices_ptr) if prices_ptr else None, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return self.last_stats
+
     def solve_batch(self, a: np.ndarray, layout: int = _capi.ROW_MAJOR, **options) -> np.ndarray:
         """a: [batch, rows, cols] float32 (layout ROW_MAJOR) or [batch, cols, rows] memory
         order (COL_MAJOR, pass the array as [batch, rows, cols] logical shape with
@@ -231,8 +265,21 @@ class Auction:
     """LSAP::Auction<Scalar, MatrixType> (Auction.h:19-44): `Auction.solve(a)` -> Edges."""
 
     @staticmethod
-    def solve(a: np.ndarray, handle: Optional[Handle] = None, **options) -> np.ndarray:
+    def solve(a, handle: Optional[Handle] = None, **options) -> np.ndarray:
+        """a: a dense numpy matrix, or a scipy.sparse matrix (the reference's SparseMatrix<Scalar, RowMajor>
+        instantiation, Auction.h:166-198: stored entries are the edges)."""
         h = handle or default_handle()
+        if hasattr(a, "tocsr") and not isinstance(a, np.ndarray):
+            m = a.tocsr()
+            if not m.has_sorted_indices:
+                m = m.sorted_indices()
+            rows, cols = m.shape
+            r2c = h.solve_csr(m.data, m.indptr, m.indices, rows, cols, **options)
+            e = np.empty(rows, EDGE_DTYPE_F64 if m.dtype == np.float64 else EDGE_DTYPE_F32)
+            e["x"] = np.arange(rows, dtype=np.uint64)
+            e["y"] = r2c.astype(np.uint64)
+            e["v"] = np.asarray(m[np.arange(rows), r2c]).ravel()  # the stored value (Auction.h:273,283)
+            return e
         r2c = h.solve(a, **options)
         return edges_from_assignment(a, r2c)
 

@@ -4,6 +4,7 @@
  *
  *   LSAP::Auction<Scalar, MatrixType>::solve(const MatrixType&)            Auction.h:19-44
  *   LSAP::AuctionMT<Scalar, MatrixType>::solve(const MatrixType&, size_t)  AuctionMT.h:24-50
+ *   LSAP::Auction<Scalar, Eigen::SparseMatrix<Scalar, Eigen::RowMajor>>::solve   Auction.h:166-198
  *   LSAP::AuctionCommon<Scalar>::Edge / Edges                             AuctionCommon.h:30-40
  *
  * so a caller such as the reference's driver (LSAP.cpp:41-45,56) only changes the class name:
@@ -85,6 +86,31 @@ inline int solve_raw(b200lsap_handle* h, const double* a, int64_t r, int64_t c, 
     return b200lsap_solve_f64(h, a, r, c, ld, layout, o, out, nullptr, st);
 }
 
+inline int solve_csr_raw(b200lsap_handle* h, const float* v, const int32_t* rp, const int32_t* ci, int64_t r, int64_t c,
+                         int64_t nnz, const b200lsap_options* o, int64_t* out, b200lsap_stats* st)
+{
+    return b200lsap_solve_csr_f32(h, v, rp, ci, r, c, nnz, o, out, nullptr, st);
+}
+inline int solve_csr_raw(b200lsap_handle* h, const double* v, const int32_t* rp, const int32_t* ci, int64_t r, int64_t c,
+                         int64_t nnz, const b200lsap_options* o, int64_t* out, b200lsap_stats* st)
+{
+    return b200lsap_solve_csr_f64(h, v, rp, ci, r, c, nnz, o, out, nullptr, st);
+}
+
+/* a compressed sparse matrix type (Eigen::SparseMatrix): it has innerIndexPtr() */
+template <typename M> struct is_sparse
+{
+    template <typename U> static char test(decltype(((const U*)0)->innerIndexPtr())*);
+    template <typename U> static long test(...);
+    enum
+    {
+        value = sizeof(test<M>(0)) == sizeof(char)
+    };
+};
+template <bool B> struct bool_tag
+{
+};
+
 } // namespace b200detail
 
 template <typename Scalar = double, typename MatrixType = void> class AuctionB200
@@ -93,9 +119,19 @@ public:
     typedef typename B200Types<Scalar>::Edge Edge;
     typedef typename B200Types<Scalar>::Edges Edges;
 
-    /* Replaces Auction<Scalar,MatrixType>::solve (Auction.h:44).  opts / stats optional. */
+    /* Replaces Auction<Scalar,MatrixType>::solve (Auction.h:44) for a dense matrix and for
+     * Eigen::SparseMatrix<Scalar, Eigen::RowMajor> (findForward on stored entries, Auction.h:166-198;
+     * the driver's Auction<double, SparseMatrix<double, RowMajor>>::solve(s), LSAP.cpp:51).
+     * opts / stats optional. */
     template <typename M>
     static const Edges solve(const M& a, const b200lsap_options* opts = nullptr, b200lsap_stats* stats = nullptr)
+    {
+        return solve_impl(a, opts, stats, b200detail::bool_tag<b200detail::is_sparse<M>::value>());
+    }
+
+private:
+    template <typename M>
+    static const Edges solve_impl(const M& a, const b200lsap_options* opts, b200lsap_stats* stats, b200detail::bool_tag<false>)
     {
         const int64_t rows = (int64_t)a.rows(), cols = (int64_t)a.cols();
         Edges E;
@@ -115,6 +151,36 @@ public:
             E[(size_t)i].x = (size_t)i;
             E[(size_t)i].y = (size_t)row_to_col[(size_t)i];
             E[(size_t)i].v = a(i, row_to_col[(size_t)i]); /* from the caller's matrix: Auction.h:273,283 */
+        }
+        return E;
+    }
+
+    /* compressed row-major sparse matrix (the reference asserts isCompressed(), Auction.h:170) */
+    template <typename M>
+    static const Edges solve_impl(const M& a, const b200lsap_options* opts, b200lsap_stats* stats, b200detail::bool_tag<true>)
+    {
+        static_assert(M::IsRowMajor, "the reference's sparse path is row-major (Auction.h:166)");
+        static_assert(sizeof(*((const M*)0)->innerIndexPtr()) == 4, "StorageIndex must be a 32-bit integer");
+        const int64_t rows = (int64_t)a.rows(), cols = (int64_t)a.cols();
+        Edges E;
+        if (rows == 0 || cols == 0)
+            return E;
+        if (!a.isCompressed())
+            throw std::runtime_error("AuctionB200::solve: the sparse matrix must be compressed (makeCompressed())");
+        std::vector<int64_t> row_to_col((size_t)rows, -1);
+        b200lsap_handle* h = b200detail::thread_handle();
+        const Scalar* values = a.valuePtr();
+        const int rc = b200detail::solve_csr_raw(h, values, (const int32_t*)a.outerIndexPtr(),
+                                                 (const int32_t*)a.innerIndexPtr(), rows, cols, (int64_t)a.nonZeros(),
+                                                 opts, row_to_col.data(), stats);
+        if (rc != B200LSAP_OK)
+            throw std::runtime_error(std::string("AuctionB200::solve: ") + b200lsap_last_error(h));
+        E.resize((size_t)rows);
+        for (int64_t i = 0; i < rows; ++i)
+        {
+            E[(size_t)i].x = (size_t)i;
+            E[(size_t)i].y = (size_t)row_to_col[(size_t)i];
+            E[(size_t)i].v = a.coeff(i, row_to_col[(size_t)i]); /* the stored value: Auction.h:273,283 */
         }
         return E;
     }

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define B200LSAP_VERSION 101
+#define B200LSAP_VERSION 102
 
 #define B200LSAP_COL_MAJOR 0 /* Eigen::Matrix default: a(i,j) = a[i + j*ld] */
 #define B200LSAP_ROW_MAJOR 1 /* a(i,j) = a[i*ld + j] */
@@ -138,6 +138,36 @@ int b200lsap_solve_device_f32(b200lsap_handle* handle, const float* a_dev, int64
 int b200lsap_solve_device_f64(b200lsap_handle* handle, const double* a_dev, int64_t rows, int64_t cols,
                               int64_t ld, int layout, const b200lsap_options* opts, int32_t* row_to_col_dev,
                               double* prices_dev, b200lsap_stats* stats);
+
+/*
+ * Replaces Auction<Scalar, Eigen::SparseMatrix<Scalar, Eigen::RowMajor>>::solve (findForward on the
+ * stored entries of a row, Auction.h:166-198, under the controller of Auction.h:44-109; the
+ * driver's second call, LSAP.cpp:36-38,51).  The matrix is compressed row-major: values /
+ * col_idx / row_ptr are Eigen's valuePtr() / innerIndexPtr() / outerIndexPtr() of a compressed
+ * matrix (StorageIndex int), row_ptr[rows] == nnz, columns ascending inside a row.  Every
+ * stored entry is an edge (the reference's sparse scan skips nothing); a missing entry is no
+ * edge.  row_to_col, prices_out, opts and stats as in b200lsap_solve_f32; eps scaling (square
+ * problems) starts at options.eps_start or 0.25.  A row without a stored entry is reported as
+ * B200LSAP_ERR_INFEASIBLE; a problem without a perfect matching ends with B200LSAP_ERR_MAX_ROUNDS
+ * (the reference does not return in either case).  The _device variants take the three arrays
+ * in device memory, int32 row_to_col_dev and nullable prices_dev in device memory.
+ */
+int b200lsap_solve_csr_f32(b200lsap_handle* handle, const float* values, const int32_t* row_ptr,
+                           const int32_t* col_idx, int64_t rows, int64_t cols, int64_t nnz,
+                           const b200lsap_options* opts, int64_t* row_to_col, double* prices_out,
+                           b200lsap_stats* stats);
+int b200lsap_solve_csr_f64(b200lsap_handle* handle, const double* values, const int32_t* row_ptr,
+                           const int32_t* col_idx, int64_t rows, int64_t cols, int64_t nnz,
+                           const b200lsap_options* opts, int64_t* row_to_col, double* prices_out,
+                           b200lsap_stats* stats);
+int b200lsap_solve_csr_device_f32(b200lsap_handle* handle, const float* values_dev, const int32_t* row_ptr_dev,
+                                  const int32_t* col_idx_dev, int64_t rows, int64_t cols, int64_t nnz,
+                                  const b200lsap_options* opts, int32_t* row_to_col_dev, double* prices_dev,
+                                  b200lsap_stats* stats);
+int b200lsap_solve_csr_device_f64(b200lsap_handle* handle, const double* values_dev, const int32_t* row_ptr_dev,
+                                  const int32_t* col_idx_dev, int64_t rows, int64_t cols, int64_t nnz,
+                                  const b200lsap_options* opts, int32_t* row_to_col_dev, double* prices_dev,
+                                  b200lsap_stats* stats);
 
 /*
  * Batched mode for MHT-style data association: `batch` independent rows x cols problems,

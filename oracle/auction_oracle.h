@@ -55,6 +55,19 @@ int oracle_auction_f32(const float* a, int64_t rows, int64_t cols, int64_t ld, i
                        int64_t max_bids, int64_t* edge_x, int64_t* edge_y, float* edge_v,
                        int64_t* n_edges, float* prices_out, float* profits_out, oracle_stats* stats);
 
+/* Auction<Scalar, Eigen::SparseMatrix<Scalar, Eigen::RowMajor>>::solve (Auction.h:166-198 under the
+ * same controller) on a compressed row-major matrix: values / col_idx / row_ptr are Eigen's
+ * valuePtr() / innerIndexPtr() / outerIndexPtr(), columns ascending inside a row.  Every stored
+ * entry is an edge. */
+int oracle_auction_csr_f64(const double* values, const int32_t* row_ptr, const int32_t* col_idx,
+                           int64_t rows, int64_t cols, int64_t max_bids, int64_t* edge_x, int64_t* edge_y,
+                           double* edge_v, int64_t* n_edges, double* prices_out, double* profits_out,
+                           oracle_stats* stats);
+int oracle_auction_csr_f32(const float* values, const int32_t* row_ptr, const int32_t* col_idx,
+                           int64_t rows, int64_t cols, int64_t max_bids, int64_t* edge_x, int64_t* edge_y,
+                           float* edge_v, int64_t* n_edges, float* prices_out, float* profits_out,
+                           oracle_stats* stats);
+
 /* Synthetic inputs (include/b200lsap_gen.h): fills a rows x cols matrix with leading
  * dimension ld in the given layout. */
 void oracle_generate_f32(float* a, int64_t rows, int64_t cols, int64_t ld, int layout, uint64_t seed,

@@ -10,10 +10,12 @@
  * What is restated (all line numbers relative to /root/reference/AuctionAlgorithm/):
  *   orc_best_two_*      Auction.h:124-152   findForward, dense: strict '>' top-2 over one row,
  *                                           a == 0 skipped, second best may equal best on ties
+ *                       Auction.h:166-198   findForward, sparse row-major (CSR): the same over the
+ *                                           stored entries of the row, in storage order, none skipped
  *   orc_forward_sweep_* Auction.h:210-306   forward: one Gauss-Seidel sweep over unlocked rows;
  *                                           bid = a - w + eps (:250), profit = w - eps (:253),
  *                                           lambda test (:257), edge-list eviction scan (:264-285)
- *   orc_best_two_col_*  Auction.h:308-334   findReverse
+ *   orc_best_two_col_*  Auction.h:308-334   findReverse (a.coeff(i, j): for CSR a search in row i)
  *   orc_reverse_sweep_* Auction.h:346-469   reverse, including the lambda rescaling of case 2
  *   orc_solve_*         Auction.h:44-109    controller: lambda = 0, eps = 1e-5 / cols
  *                                           (internal.h:16), prices 0, profits 1, steps 1-3
@@ -35,6 +37,8 @@ typedef struct
     const ORC_T* a;
     int64_t rows, cols;
     int64_t rs, cs; /* element strides: a(i,j) = a[i*rs + j*cs] */
+    const int32_t* csr_ptr; /* non-NULL: a holds the stored values of a compressed row-major sparse */
+    const int32_t* csr_col; /* matrix (Eigen outerIndexPtr / innerIndexPtr), columns ascending in a row */
     ORC_T* prices;
     ORC_T* profits;
     unsigned char* row_locked;
@@ -53,6 +57,28 @@ static int ORC_FN(orc_best_two_)(const ORC_FN(orc_state_) * s, int64_t i, ORC_T*
                                  ORC_T* a_best, int64_t* j_i)
 {
     int found = 0;
+    if (s->csr_ptr)
+    {
+        /* Auction.h:166-198 */
+        for (int32_t k = s->csr_ptr[i]; k < s->csr_ptr[i + 1]; k++)
+        {
+            const int64_t j = s->csr_col[k];
+            const ORC_T aij = s->a[k];
+            const ORC_T diff = aij - s->prices[j];
+            if (diff > *v_i)
+            {
+                if (found)
+                    *w_i = *v_i;
+                *v_i = diff;
+                *j_i = j;
+                *a_best = aij;
+                found = 1;
+            }
+            if (diff > *w_i && *j_i != j)
+                *w_i = diff;
+        }
+        return found;
+    }
     const ORC_T* row = s->a + i * s->rs;
     const int64_t cs = s->cs;
     for (int64_t j = 0; j < s->cols; j++)
@@ -134,15 +160,30 @@ static int ORC_FN(orc_forward_sweep_)(ORC_FN(orc_state_) * s)
     return any;
 }
 
+/* a.coeff(i, j) of the compressed sparse matrix: 0 when (i, j) is not stored */
+static ORC_T ORC_FN(orc_csr_coeff_)(const ORC_FN(orc_state_) * s, int64_t i, int64_t j)
+{
+    int32_t lo = s->csr_ptr[i], hi = s->csr_ptr[i + 1];
+    while (lo < hi)
+    {
+        const int32_t mid = lo + (hi - lo) / 2;
+        if (s->csr_col[mid] < j)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    return (lo < s->csr_ptr[i + 1] && s->csr_col[lo] == j) ? s->a[lo] : (ORC_T)0;
+}
+
 /* Auction.h:308-334 */
 static int ORC_FN(orc_best_two_col_)(const ORC_FN(orc_state_) * s, int64_t j, ORC_T* b_j, ORC_T* g_j,
                                      ORC_T* a_best, int64_t* i_j)
 {
     int found = 0;
-    const ORC_T* col = s->a + j * s->cs;
+    const ORC_T* col = s->csr_ptr ? NULL : s->a + j * s->cs;
     for (int64_t i = 0; i < s->rows; i++)
     {
-        const ORC_T aij = col[i * s->rs];
+        const ORC_T aij = s->csr_ptr ? ORC_FN(orc_csr_coeff_)(s, i, j) : col[i * s->rs];
         if (aij == 0)
             continue;
         const ORC_T diff = aij - s->profits[i];
@@ -242,9 +283,10 @@ static int ORC_FN(orc_free_cols_at_most_lambda_)(const ORC_FN(orc_state_) * s)
 }
 
 /* Auction.h:44-109 */
-int ORC_FN(oracle_auction_)(const ORC_T* a, int64_t rows, int64_t cols, int64_t ld, int layout,
-                            int64_t max_bids, int64_t* edge_x, int64_t* edge_y, ORC_T* edge_v,
-                            int64_t* n_edges, ORC_T* prices_out, ORC_T* profits_out, oracle_stats* stats)
+static int ORC_FN(orc_solve_)(const ORC_T* a, const int32_t* csr_ptr, const int32_t* csr_col, int64_t rows,
+                              int64_t cols, int64_t ld, int layout, int64_t max_bids, int64_t* edge_x,
+                              int64_t* edge_y, ORC_T* edge_v, int64_t* n_edges, ORC_T* prices_out,
+                              ORC_T* profits_out, oracle_stats* stats)
 {
     oracle_stats local;
     ORC_FN(orc_state_) s;
@@ -255,6 +297,8 @@ int ORC_FN(oracle_auction_)(const ORC_T* a, int64_t rows, int64_t cols, int64_t 
     if (rows <= 0 || cols <= 0)
         return ORC_OK;
     s.a = a;
+    s.csr_ptr = csr_ptr;
+    s.csr_col = csr_col;
     s.rows = rows;
     s.cols = cols;
     s.rs = layout == ORACLE_ROW_MAJOR ? ld : 1;
@@ -320,6 +364,25 @@ int ORC_FN(oracle_auction_)(const ORC_T* a, int64_t rows, int64_t cols, int64_t 
     free(s.col_locked);
     s.st->status = status;
     return status;
+}
+
+int ORC_FN(oracle_auction_)(const ORC_T* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                            int64_t max_bids, int64_t* edge_x, int64_t* edge_y, ORC_T* edge_v,
+                            int64_t* n_edges, ORC_T* prices_out, ORC_T* profits_out, oracle_stats* stats)
+{
+    return ORC_FN(orc_solve_)(a, NULL, NULL, rows, cols, ld, layout, max_bids, edge_x, edge_y, edge_v, n_edges,
+                              prices_out, profits_out, stats);
+}
+
+/* Auction<Scalar, Eigen::SparseMatrix<Scalar, Eigen::RowMajor>>::solve on a compressed matrix:
+ * values / col_idx / row_ptr = valuePtr() / innerIndexPtr() / outerIndexPtr() */
+int ORC_FN(oracle_auction_csr_)(const ORC_T* values, const int32_t* row_ptr, const int32_t* col_idx,
+                                int64_t rows, int64_t cols, int64_t max_bids, int64_t* edge_x,
+                                int64_t* edge_y, ORC_T* edge_v, int64_t* n_edges, ORC_T* prices_out,
+                                ORC_T* profits_out, oracle_stats* stats)
+{
+    return ORC_FN(orc_solve_)(values, row_ptr, col_idx, rows, cols, 0, ORACLE_ROW_MAJOR, max_bids, edge_x, edge_y,
+                              edge_v, n_edges, prices_out, profits_out, stats);
 }
 
 #undef ORC_CAT2

@@ -55,6 +55,11 @@ def oracle() -> C.CDLL:
             fn.restype = C.c_int
             fn.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_void_p,
                            C.c_void_p, C.c_void_p, _i64p, C.c_void_p, C.c_void_p, C.POINTER(OracleStats)]
+        for name in ("oracle_auction_csr_f64", "oracle_auction_csr_f32"):
+            fn = getattr(lib, name)
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p,
+                           C.c_void_p, C.c_void_p, _i64p, C.c_void_p, C.c_void_p, C.POINTER(OracleStats)]
         for name in ("oracle_generate_f32", "oracle_generate_f64"):
             fn = getattr(lib, name)
             fn.restype = None
@@ -156,6 +161,54 @@ def reference_solve(a: np.ndarray, variant: str = "auction", n_threads: int = 2)
                                   ey.ctypes.data, ev.ctypes.data, C.byref(sec))
     else:
         raise ValueError(variant)
+    return dict(x=ex[:n].copy(), y=ey[:n].copy(), v=ev[:n].copy(), seconds=sec.value)
+
+
+def _csr_arrays(values, row_ptr, col_idx):
+    values = np.ascontiguousarray(values)
+    assert values.dtype in (np.float32, np.float64)
+    return values, np.ascontiguousarray(row_ptr, np.int32), np.ascontiguousarray(col_idx, np.int32)
+
+
+def oracle_solve_csr(values, row_ptr, col_idx, rows: int, cols: int, max_bids: int = -1, want_prices: bool = False):
+    """The C restatement of Auction<S, SparseMatrix<S, RowMajor>>::solve in values' own dtype."""
+    lib = oracle()
+    values, row_ptr, col_idx = _csr_arrays(values, row_ptr, col_idx)
+    cap = max(rows, cols)
+    ex = np.empty(cap, np.int64)
+    ey = np.empty(cap, np.int64)
+    ev = np.empty(cap, values.dtype)
+    ne = C.c_int64(0)
+    st = OracleStats()
+    prices = np.empty(cols, values.dtype) if want_prices else None
+    profits = np.empty(rows, values.dtype) if want_prices else None
+    fn = lib.oracle_auction_csr_f64 if values.dtype == np.float64 else lib.oracle_auction_csr_f32
+    status = fn(values.ctypes.data, row_ptr.ctypes.data, col_idx.ctypes.data, rows, cols, max_bids, ex.ctypes.data,
+                ey.ctypes.data, ev.ctypes.data, C.byref(ne), prices.ctypes.data if want_prices else None,
+                profits.ctypes.data if want_prices else None, C.byref(st))
+    n = ne.value
+    out = dict(x=ex[:n].copy(), y=ey[:n].copy(), v=ev[:n].copy(), status=status, stats=st.as_dict())
+    if want_prices:
+        out["prices"], out["profits"] = prices, profits
+    return out
+
+
+def reference_solve_csr(values, row_ptr, col_idx, rows: int, cols: int):
+    """The unmodified reference's sparse instantiation (double)."""
+    lib = reference()
+    if lib is None or not hasattr(lib, "ref_auction_csr_f64"):
+        raise RuntimeError("oracle/_ref/libref_auction.so lacks ref_auction_csr_f64 (rebuild where /root/reference exists)")
+    values, row_ptr, col_idx = _csr_arrays(np.asarray(values, np.float64), row_ptr, col_idx)
+    cap = max(rows, cols)
+    ex = np.empty(cap, np.int64)
+    ey = np.empty(cap, np.int64)
+    ev = np.empty(cap, np.float64)
+    sec = C.c_double(0)
+    lib.ref_auction_csr_f64.restype = C.c_int64
+    lib.ref_auction_csr_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+    n = lib.ref_auction_csr_f64(values.ctypes.data, row_ptr.ctypes.data, col_idx.ctypes.data, rows, cols,
+                                ex.ctypes.data, ey.ctypes.data, ev.ctypes.data, C.byref(sec))
     return dict(x=ex[:n].copy(), y=ey[:n].copy(), v=ev[:n].copy(), seconds=sec.value)
 
 

@@ -105,4 +105,20 @@ int64_t ref_auction_f32_as_f64(const float* a, int64_t rows, int64_t cols, int64
     return flatten<double>(edges, ex, ey, ev);
 }
 
+/* Auction<double, SparseMatrix<double, RowMajor>>::solve (the driver's second call, LSAP.cpp:36-38,51)
+ * on a compressed row-major matrix given as Eigen's own three arrays. */
+int64_t ref_auction_csr_f64(const double* values, const int32_t* row_ptr, const int32_t* col_idx, int64_t rows,
+                            int64_t cols, int64_t* ex, int64_t* ey, double* ev, double* seconds_out)
+{
+    typedef Eigen::SparseMatrix<double, Eigen::RowMajor> Sp;
+    const int64_t nnz = row_ptr[rows];
+    const Sp m = Eigen::Map<const Sp>(rows, cols, nnz, row_ptr, col_idx, values);
+    const auto t0 = std::chrono::steady_clock::now();
+    const auto edges = LSAP::Auction<double, Sp>::solve(m);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+    return flatten<double>(edges, ex, ey, ev);
+}
+
 } // extern "C"

@@ -1,7 +1,8 @@
 // Test program for include/AuctionB200.h.
 //   default build: a minimal dense matrix class (the GPU box has no Eigen);
 //   -DWITH_REFERENCE_EIGEN: the reference's own headers and Eigen types (compile check here).
-// Usage: wrapper_demo rows cols seed [rowmajor] -> prints "x y v" per edge, then "objective <sum>".
+// Usage: wrapper_demo rows cols seed [rowmajor|sparse] -> prints "x y v" per edge, then "objective <sum>".
+//   sparse: a compressed row-major matrix keeping entry (i, j) when j == i or (i * 7 + j * 13) % 4 != 0.
 #ifdef WITH_REFERENCE_EIGEN
 #include "AuctionAlgorithm/Auction.h"
 #include "AuctionAlgorithm/AuctionMT.h"
@@ -25,6 +26,42 @@ template <typename S, bool RowMajor> struct MiniMatrix
     size_t outerStride() const { return RowMajor ? c : r; }
     S& operator()(size_t i, size_t j) { return RowMajor ? d[i * c + j] : d[i + j * r]; }
     const S& operator()(size_t i, size_t j) const { return RowMajor ? d[i * c + j] : d[i + j * r]; }
+};
+
+// what AuctionB200 needs of Eigen::SparseMatrix<S, RowMajor> (compressed)
+template <typename S> struct MiniSparse
+{
+    enum { IsRowMajor = 1 };
+    size_t r, c;
+    std::vector<int> ptr, idx;
+    std::vector<S> val;
+    template <typename D> explicit MiniSparse(const D& d) : r(d.rows()), c(d.cols()), ptr(1, 0)
+    {
+        for (size_t i = 0; i < r; ++i)
+        {
+            for (size_t j = 0; j < c; ++j)
+                if (j == i || (i * 7 + j * 13) % 4 != 0)
+                {
+                    idx.push_back((int)j);
+                    val.push_back(d(i, j));
+                }
+            ptr.push_back((int)idx.size());
+        }
+    }
+    size_t rows() const { return r; }
+    size_t cols() const { return c; }
+    bool isCompressed() const { return true; }
+    size_t nonZeros() const { return val.size(); }
+    const S* valuePtr() const { return val.data(); }
+    const int* innerIndexPtr() const { return idx.data(); }
+    const int* outerIndexPtr() const { return ptr.data(); }
+    S coeff(size_t i, size_t j) const
+    {
+        for (int k = ptr[i]; k < ptr[i + 1]; ++k)
+            if (idx[k] == (int)j)
+                return val[k];
+        return S(0);
+    }
 };
 
 template <typename M> void fill(M& m, uint64_t seed)
@@ -52,7 +89,8 @@ int main(int argc, char** argv)
         return 2;
     const size_t rows = atol(argv[1]), cols = atol(argv[2]);
     const uint64_t seed = atol(argv[3]);
-    const bool rowmajor = argc > 4;
+    const bool sparse = argc > 4 && argv[4][0] == 's';
+    const bool rowmajor = argc > 4 && !sparse;
     try
     {
 #ifdef WITH_REFERENCE_EIGEN
@@ -63,9 +101,21 @@ int main(int argc, char** argv)
         Eigen::MatrixXf mf = m.cast<float>();
         LSAP::Auction<float, Eigen::MatrixXf>::Edges sf = LSAP::AuctionB200<float>::solve(mf);
         (void)sf;
+        Eigen::SparseMatrix<double, Eigen::RowMajor> sp(rows, cols);
+        sp = m.sparseView();
+        sp.makeCompressed();
+        LSAP::Auction<double>::Edges ss = LSAP::AuctionB200<double>::solve(sp);         // cf. LSAP.cpp:51
+        (void)ss;
         print(solution);
 #else
-        if (rowmajor)
+        if (sparse)
+        {
+            MiniMatrix<double, true> m(rows, cols);
+            fill(m, seed);
+            const MiniSparse<double> sp(m);
+            print(LSAP::AuctionB200<double>::solve(sp));
+        }
+        else if (rowmajor)
         {
             MiniMatrix<float, true> m(rows, cols);
             fill(m, seed);

@@ -65,3 +65,20 @@ def check_parity(a, r2c, prices, ref_r2c, eps_final):
     if free.any():
         assert prices[free].max() <= prices[~free].min(), "an unassigned column is priced above an assigned one"
     return "within-bound"
+
+
+# ---- compressed row-major sparse inputs (the reference's SparseMatrix<Scalar, RowMajor> path) -----------
+def make_csr(rows, cols, seed, dtype=np.float64, mod=4, thr=1):
+    """Values of the counter-based generator (include/b200lsap_gen.h) at the kept positions:
+    (i, j) is stored when j == i (a perfect matching always exists) or (7 i + 13 j) % mod >= thr.
+    Returns (dense with zeros at missing entries, values, row_ptr, col_idx)."""
+    from oracle import pyoracle as po
+    a = po.generate(rows, cols, seed).astype(dtype)
+    i = np.arange(rows)[:, None]
+    j = np.arange(cols)[None, :]
+    keep = (j == i) | ((7 * i + 13 * j) % mod >= thr)
+    a = np.where(keep, a, 0).astype(dtype)
+    row_ptr = np.concatenate([[0], np.cumsum(keep.sum(axis=1))]).astype(np.int32)
+    col_idx = np.nonzero(keep)[1].astype(np.int32)
+    values = a[keep]
+    return a, values, row_ptr, col_idx

@@ -58,6 +58,27 @@ if __name__ == "__main__":
         nb = 16384 * 16384 * 4
         print(f"sweep2: zero prices min {min(a):.4f} mean {sum(a[3:])/5:.4f} ms -> {nb/min(a)/1e6:.0f} GB/s | last prices min {min(b):.4f} "
               f"mean {sum(b[3:])/5:.4f} ms -> {nb/(sum(b[3:])/5)/1e6:.0f} GB/s | solve {st['ms_solve']:.2f} ms", flush=True)
+    if "sparse" in which:
+        import scipy.sparse as sp
+        for n, per_row in ((5000, 5000), (20000, 40), (200000, 32), (1000000, 16)):
+            rng = np.random.default_rng(1)
+            if per_row >= n:
+                a = (rng.integers(0, 1 << 24, (n, n)) + 1).astype(np.float64) / float(1 << 24)
+                m = sp.csr_matrix(a)
+            else:
+                ci = rng.integers(0, n, (n, per_row)); ci[:, 0] = rng.permutation(n); ci.sort(axis=1)
+                keep = np.ones_like(ci, bool); keep[:, 1:] = ci[:, 1:] != ci[:, :-1]
+                rp = np.concatenate([[0], np.cumsum(keep.sum(axis=1))]).astype(np.int32)
+                vals = (rng.integers(0, 1 << 24, int(keep.sum())) + 1) / float(1 << 24)
+                m = sp.csr_matrix((vals, ci[keep].astype(np.int32), rp), shape=(n, n))
+            for dt in (np.float64, np.float32):
+                v = m.data.astype(dt)
+                for _ in range(2):
+                    t0 = time.time(); r2c = h.solve_csr(v, m.indptr, m.indices, n, n); wall = time.time() - t0
+                st = h.last_stats
+                print(f"sparse {n}x{n} nnz {m.nnz} {dt.__name__}: solve {st['ms_solve']:.2f} ms (upload {st['ms_upload']:.1f}, wall {wall*1e3:.1f}) "
+                      f"rounds {st['rounds']} narrow {st['narrow_rounds']} bids {st['bids']} phases {st['phases']} "
+                      f"objective {m[np.arange(n), r2c].sum():.6f}", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
     if "c4f" in which:

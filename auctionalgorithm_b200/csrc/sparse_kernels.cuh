@@ -15,8 +15,11 @@
 // whole grid (lanes stride the row's entries: 8- or 12-byte (column, value) pairs, coalesced; prices
 // are gathered from L2) with two grid syncs.  Rounds only ever get narrower inside an eps phase, so
 // once a round's bidders fit one CTA (csr_narrow_limit: by their number and by the entries they
-// will read) CTA 0 finishes the phase alone with block barriers while the other CTAs wait at one
-// grid sync.
+// will read) CTA 0 finishes the phase alone (csr_narrow_episode) while the other CTAs wait at one
+// grid sync: bidder list, bids and the per-column resolve live in shared memory (a hash table keyed
+// by column with a compare-and-swap argmax: highest bid, lowest row among equal bids), the matrix
+// entries come through L1 (read-only for the whole solve), prices and owners are only written by
+// this CTA, so a round is three block barriers and no global atomic.
 #pragma once
 
 namespace b200lsap
@@ -104,7 +107,234 @@ __device__ __forceinline__ void csr_bid_row(const DenseState<T>& s, const CsrVie
 __device__ __forceinline__ int csr_narrow_limit(long long nnz, int rows)
 {
     const long long avg = max(1ll, nnz / max(rows, 1));
-    return (int)min((long long)kThreads, max(32ll, (256ll * 1024) / avg));
+    return (int)min((long long)kThreads, max(1ll, (64ll * 1024) / avg));
+}
+
+// ---------------------------------------------------------------------------------------------
+// One CTA finishes an eps phase (n <= kThreads bidders; rounds never get wider inside a phase).
+// ---------------------------------------------------------------------------------------------
+constexpr int kCsrHash = 2048; // >= 2 kThreads slots: open addressing stays short
+
+template <typename T> struct CsrNarrowShared
+{
+    int q[2][kThreads];      // bidder rows of this round / the next
+    int bcol[kThreads];      // column bidder k bids for
+    double bbid[kThreads];   // its bid
+    int hcol[kCsrHash];      // hash table: column, -1 empty
+    int hbest[kCsrHash];     //             bidder index of the best bid so far, -1 none
+    Top2<T> part[kWarpsPerBlock]; // long rows: partial results of the row's segments
+    int qn[2];               // bidders in q[0] / q[1]
+    int status;
+    double pmax;
+};
+
+// bidder x is a better bid than bidder y for the same column (Jacobi resolve: highest bid, lowest row)
+template <typename T> __device__ __forceinline__ bool csr_better(const CsrNarrowShared<T>& sh, const int* q, int x, int y)
+{
+    const double bx = sh.bbid[x], by = sh.bbid[y];
+    return bx > by || (bx == by && q[x] < q[y]);
+}
+
+// One warp: top-2 of entries [k0, k1) of a row (a segment or all of it), every lane ends with it.
+template <typename T, bool kDeep>
+__device__ __forceinline__ Top2<T> csr_scan_range(const CsrView<T>& m, const double* prices, int k0, int k1, int lane)
+{
+    Top2<T> t = top2_empty<T, kDeep>();
+    for (int k = k0 + lane; k < k1; k += 64) // two independent gathers in flight per lane
+    {
+        const int j0 = __ldg(m.col + k);
+        const T a0 = __ldg(m.val + k);
+        const bool two = k + 32 < k1;
+        const int j1 = two ? __ldg(m.col + k + 32) : 0;
+        const T a1 = two ? __ldg(m.val + k + 32) : T(0);
+        // prices are written by this CTA only during the episode: plain loads (L1) stay coherent
+        const double p0 = prices[j0];
+        const double p1 = two ? prices[j1] : 0.0;
+        top2_push_stored(t, a0, p0, j0);
+        if (two)
+            top2_push_stored(t, a1, p1, j1);
+    }
+    top2_warp_reduce(t);
+    return t;
+}
+
+// All lanes of one warp hold the row's top-2: place bidder k's bid in shared memory.
+template <typename T>
+__device__ __forceinline__ void csr_post_bid(const DenseState<T>& s, const CsrView<T>& m, CsrNarrowShared<T>& sh, int k, int i,
+                                             Top2<T> t, double eps, int lane)
+{
+    if (t.j < 0 && m.ptr[i + 1] > m.ptr[i])
+    {
+        // every value at or below -1e6: the rescue of the dense path's rescue_scan
+        t = csr_scan_range<T, true>(m, s.prices, m.ptr[i], m.ptr[i + 1], lane);
+        if (t.j >= 0 && t.w == -CUDART_INF)
+            t.w = fmin(-kNoSecondBest, t.v);
+    }
+    if (lane == 0)
+    {
+        if (t.j < 0)
+        {
+            sh.status = 2; // B200LSAP_ERR_INFEASIBLE
+            sh.bcol[k] = -1;
+            return;
+        }
+        const double bid = (double)t.a - t.w + eps; // Auction.h:250
+        s.profits[i] = t.w - eps;                   // Auction.h:253
+        sh.bcol[k] = t.j;
+        sh.bbid[k] = bid;
+        if (bid > sh.pmax)
+            atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax), (unsigned long long)__double_as_longlong(bid));
+    }
+}
+
+// Returns the rounds played; *bids_out their bidders.  On return sh.qn[buf] bidders are left (0: phase done).
+template <typename T>
+__device__ __noinline__ long long csr_narrow_episode(const DenseState<T>& s, const CsrView<T>& m, CsrNarrowShared<T>& sh,
+                                                     const int* list, int n0, double eps, double pmax0, long long budget,
+                                                     long long* bids_out)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int k = tid; k < kCsrHash; k += kThreads)
+    {
+        sh.hcol[k] = -1;
+        sh.hbest[k] = -1;
+    }
+    if (tid < n0)
+        sh.q[0][tid] = list[tid];
+    if (tid == 0)
+    {
+        sh.qn[0] = n0;
+        sh.qn[1] = 0;
+        sh.status = 0;
+        sh.pmax = pmax0;
+    }
+    __syncthreads();
+    const long long avg = max(1ll, m.nnz / max(s.rows, 1));
+    int buf = 0, my_h = -1;
+    long long rounds = 0, bids = 0;
+    for (;;)
+    {
+        const int n = sh.qn[buf];
+        if (n == 0 || rounds >= budget)
+            break;
+        const int* q = sh.q[buf];
+        int* qnext = sh.q[buf ^ 1];
+        // ---- bids ----------------------------------------------------------------------------------
+        // long rows and few bidders: S warps share a row (segments of >= 64 entries on average)
+        int S = 1;
+        while (S * 2 * n <= kWarpsPerBlock && avg >= 128ll * S)
+            S *= 2;
+        if (S == 1)
+        {
+            for (int k = warp; k < n; k += kWarpsPerBlock)
+            {
+                const int i = q[k];
+                const Top2<T> t = csr_scan_range<T, false>(m, s.prices, m.ptr[i], m.ptr[i + 1], lane);
+                csr_post_bid<T>(s, m, sh, k, i, t, eps, lane);
+            }
+        }
+        else
+        {
+            const int k = warp / S, sg = warp - k * S;
+            if (k < n)
+            {
+                const int i = q[k];
+                const int r0 = m.ptr[i], r1 = m.ptr[i + 1];
+                const int len = (r1 - r0 + S - 1) / S;
+                const int k0 = min(r0 + sg * len, r1), k1 = min(k0 + len, r1);
+                const Top2<T> t = csr_scan_range<T, false>(m, s.prices, k0, k1, lane);
+                if (lane == 0)
+                    sh.part[warp] = t;
+            }
+            __syncthreads();
+            if (warp < n)
+            {
+                Top2<T> t = lane < S ? sh.part[warp * S + lane] : top2_empty<T>();
+                top2_warp_reduce(t);
+                csr_post_bid<T>(s, m, sh, warp, q[warp], t, eps, lane);
+            }
+        }
+        if (tid == 0)
+            sh.qn[buf ^ 1] = 0;
+        __syncthreads();
+        if (sh.status != 0)
+            break;
+        // ---- resolve: one thread per bidder; per column the best bid by compare-and-swap ----------------
+        int col = -1;
+        if (tid < n)
+        {
+            col = sh.bcol[tid];
+            int h = (int)(((unsigned)col * 2654435761u) >> 21); // top 11 bits: kCsrHash slots
+            for (;;)
+            {
+                const int old = atomicCAS(&sh.hcol[h], -1, col);
+                if (old == -1 || old == col)
+                    break;
+                h = (h + 1) & (kCsrHash - 1);
+            }
+            my_h = h;
+            int cur = *(volatile int*)&sh.hbest[h];
+            for (;;)
+            {
+                if (cur != -1 && !csr_better(sh, q, tid, cur))
+                    break;
+                const int old = atomicCAS(&sh.hbest[h], cur, tid);
+                if (old == cur)
+                    break;
+                cur = old;
+            }
+        }
+        __syncthreads();
+        int push = -1;
+        if (tid < n)
+        {
+            const int row = q[tid];
+            if (sh.hbest[my_h] == tid)
+            {
+                const int prev = s.owner[col];
+                s.owner[col] = row;
+                s.prices[col] = sh.bbid[tid]; // Auction.h:259
+                s.row2col[row] = col;
+                if (prev >= 0)
+                    s.row2col[prev] = -1;     // Auction.h:270
+                push = prev;
+            }
+            else
+                push = row;
+        }
+        const unsigned mask = __ballot_sync(kFullMask, push >= 0);
+        if (mask)
+        {
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&sh.qn[buf ^ 1], __popc(mask));
+            base = __shfl_sync(kFullMask, base, 0);
+            if (push >= 0)
+                qnext[base + __popc(mask & ((1u << lane) - 1))] = push;
+        }
+        __syncthreads();
+        if (my_h >= 0)
+        {
+            sh.hcol[my_h] = -1; // next round's inserts come after its first barrier
+            sh.hbest[my_h] = -1;
+            my_h = -1;
+        }
+        rounds++;
+        bids += n;
+        buf ^= 1;
+    }
+    __syncthreads();
+    if (tid == 0)
+    {
+        sh.qn[0] = sh.qn[buf]; // what is left, for the caller
+        if (sh.pmax > s.ctrl->pmax)
+            s.ctrl->pmax = sh.pmax;
+        if (sh.status != 0)
+            s.ctrl->status = sh.status;
+    }
+    __syncthreads();
+    *bids_out = bids;
+    return rounds;
 }
 
 template <typename T>
@@ -118,7 +348,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_csr(const __grid_consta
     const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
     const long long n_threads = (long long)gridDim.x * kThreads;
     volatile DenseCtrl* ctrl = s.ctrl;
-    __shared__ int sh_n;
+    __shared__ CsrNarrowShared<T> nsh;
 
     int cur = 0, phase = 0;
     const int n_phases = ctrl->n_phases;
@@ -157,42 +387,22 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_csr(const __grid_consta
             // ---- CTA 0 finishes the phase: the same rounds with block barriers ----------------------
             if (blockIdx.x == 0)
             {
-                int nn = n, c = cur;
-                long long r = 0, b = 0;
-                while (nn > 0 && spent + r < max_rounds && ctrl->status == 0)
-                {
-                    if (threadIdx.x == 0)
-                        ctrl->count[c ^ 1] = 0;
-                    const double pmax = fmax(ctrl->pmax, amax);
-                    for (int k = threadIdx.x >> 5; k < nn; k += kWarpsPerBlock)
-                        csr_bid_row<T>(s, m, s.list[c][k], eps, pmax, lane);
-                    __syncthreads();
-                    if (ctrl->status != 0)
-                        break;
-                    resolve_phase<T>(s, s.list[c], nn, s.list[c ^ 1], &s.ctrl->count[c ^ 1], threadIdx.x, kThreads, lane);
-                    __syncthreads();
-                    if (threadIdx.x == 0)
-                        sh_n = ctrl->count[c ^ 1];
-                    __syncthreads();
-                    r++;
-                    b += nn;
-                    nn = sh_n;
-                    c ^= 1;
-                }
+                long long b = 0;
+                const long long r = csr_narrow_episode<T>(s, m, nsh, s.list[cur], n, eps, fmax(ctrl->pmax, amax),
+                                                          max_rounds - spent, &b);
                 if (threadIdx.x == 0)
                 {
-                    ctrl->cur = c;
                     ctrl->narrow_rounds += r;
                     ctrl->gs_bids += b; // bids of the narrow episodes (added to bids at the end)
-                    if (nn > 0 && ctrl->status == 0)
-                        ctrl->status = 3;
+                    if (nsh.qn[0] > 0 && ctrl->status == 0)
+                        ctrl->status = 3; // round budget spent
+                    ctrl->count[cur] = 0;
                     __threadfence();
                 }
             }
             grid.sync();
             if (ctrl->status != 0)
                 break;
-            cur = ctrl->cur;
             continue;
         }
         // ---- wide round: a warp per bidding row over the whole grid ---------------------------------

@@ -33,6 +33,7 @@ namespace b200lsap
 constexpr int kNarrowThreads = 512;
 constexpr int kNarrowWarps = kNarrowThreads / 32;
 constexpr int kMissMark = -2;
+constexpr int kNarrowHashBits = 9, kNarrowHash = 1 << kNarrowHashBits; // >= 2 kNarrowMax slots
 
 template <typename T> struct NarrowKShared
 {
@@ -43,6 +44,8 @@ template <typename T> struct NarrowKShared
     int prev[kNarrowMax];           // current owner of that column
     double bid[kNarrowMax];
     int warp_count[kNarrowWarps];
+    int hcol[kNarrowHash];  // resolve of a round with more than 32 bidders: column of the slot, -1 empty
+    int hbest[kNarrowHash]; //   bidder index of the best bid for it so far, -1 none
     int qn, stop, nmiss, served;
     double pmax;
     Top2<T> res; // result of the fallback scan
@@ -148,6 +151,89 @@ __device__ __forceinline__ bool narrow_eval_regs(const DenseState<T>& s, const d
     // w above the -1e6 start value of the scan (Auction.h:237) and above `bound` beats every
     // column outside the cache
     return h.count >= 2 && wmask != 0 && k2 != 0 && t.w > h.bound && t.w > -kNoSecondBest;
+}
+
+// Two bidders of one warp at once (rounds with more bidders than warps): the same steps as
+// narrow_eval_regs with the two dependency chains interleaved stage by stage, so that the latency of
+// one bidder's load, gather or reduction hides behind the other's.  Results as narrow_eval.
+template <bool kSmem, typename T>
+__device__ __forceinline__ void narrow_eval2(const DenseState<T>& s, const double* prices_s, const int* owner_s, const int (&i)[2],
+                                             int lane, Top2<T> (&t)[2], int (&prev)[2], bool (&hit)[2])
+{
+    CacheEnt<T> e[2];
+    RowCacheHdr h[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        e[u] = s.cache[(long long)i[u] * kCacheK + lane];
+        h[u] = s.cache_hdr[i[u]];
+    }
+    double p[2];
+    int own[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        if (kSmem)
+        {
+            p[u] = prices_s[e[u].col];
+            own[u] = owner_s[e[u].col];
+        }
+        else
+        {
+            p[u] = __ldcg(s.prices + e[u].col);
+            own[u] = __ldcg(s.owner + e[u].col);
+        }
+    }
+    bool valid[2], c1[2], top[2], winner[2];
+    unsigned hi[2], lo[2], mh[2], ml[2], mh2[2], ml2[2], wmask[2];
+    int mj[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        valid[u] = e[u].a != T(0) && lane < h[u].count;
+        const unsigned long long key = valid[u] ? ordered_key(widen_exact(e[u].a) - p[u]) : 0ull;
+        hi[u] = (unsigned)(key >> 32);
+        lo[u] = (unsigned)key;
+    }
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+        mh[u] = __reduce_max_sync(kFullMask, hi[u]);
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        c1[u] = valid[u] && hi[u] == mh[u];
+        ml[u] = __reduce_max_sync(kFullMask, c1[u] ? lo[u] : 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        top[u] = c1[u] && lo[u] == ml[u];
+        mj[u] = (int)__reduce_min_sync(kFullMask, top[u] ? (unsigned)e[u].col : 0xffffffffu);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        winner[u] = top[u] && e[u].col == mj[u];
+        mh2[u] = __reduce_max_sync(kFullMask, winner[u] ? 0u : hi[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+        ml2[u] = __reduce_max_sync(kFullMask, (!winner[u] && valid[u] && hi[u] == mh2[u]) ? lo[u] : 0u);
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+        wmask[u] = __ballot_sync(kFullMask, winner[u]);
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+    {
+        const int src = wmask[u] ? __ffs(wmask[u]) - 1 : 0;
+        t[u].a = __shfl_sync(kFullMask, e[u].a, src);
+        prev[u] = __shfl_sync(kFullMask, own[u], src);
+        t[u].j = wmask[u] ? mj[u] : -1;
+        t[u].v = key_to_double(((unsigned long long)mh[u] << 32) | ml[u]);
+        const unsigned long long k2 = ((unsigned long long)mh2[u] << 32) | ml2[u];
+        t[u].w = k2 ? key_to_double(k2) : -kNoSecondBest;
+        hit[u] = h[u].count >= 2 && wmask[u] != 0 && k2 != 0 && t[u].w > h[u].bound && t[u].w > -kNoSecondBest;
+    }
 }
 
 // Every thread: unfiltered scan of row i (ties, too few edges), with the -1e6 rescue of rescue_scan.
@@ -366,6 +452,11 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             rank += list[k] < mine;
         sh.q[0][rank] = mine;
     }
+    for (int k = tid; k < kNarrowHash; k += kNarrowThreads)
+    {
+        sh.hcol[k] = -1;
+        sh.hbest[k] = -1;
+    }
     if (tid == 0)
     {
         sh.qn = n;
@@ -494,25 +585,37 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         const long long t_round = clock64();
 #endif
         // ---- bids from the caches: a warp per bidder -------------------------------------------------
-        for (int b = warp; b < n; b += kNarrowWarps)
+        for (int b = warp; b < n; b += 2 * kNarrowWarps)
         {
-            const int i = q[b];
-            Top2<T> t;
-            int prev;
-            const bool hit = narrow_eval<kSmem, false, T>(s, prices_s, owner_s, i, lane, t, prev);
+            const int b1 = b + kNarrowWarps;
+            Top2<T> t[2];
+            int prev[2];
+            bool hit[2];
+            const int i[2] = {q[b], b1 < n ? q[b1] : q[b]};
+            if (b1 < n)
+                narrow_eval2<kSmem, T>(s, prices_s, owner_s, i, lane, t, prev, hit);
+            else
+                hit[0] = narrow_eval<kSmem, false, T>(s, prices_s, owner_s, i[0], lane, t[0], prev[0]);
             if (lane == 0)
             {
-                if (hit)
+#pragma unroll
+                for (int u = 0; u < 2; u++)
                 {
-                    sh.col[b] = t.j;
-                    sh.prev[b] = prev;
-                    sh.bid[b] = (double)t.a - t.w + eps; // Auction.h:250
-                    s.profits[i] = t.w - eps;            // Auction.h:253
-                }
-                else
-                {
-                    sh.col[b] = kMissMark;
-                    atomicAdd(&sh.nmiss, 1);
+                    const int bb = u ? b1 : b;
+                    if (bb >= n)
+                        break;
+                    if (hit[u])
+                    {
+                        sh.col[bb] = t[u].j;
+                        sh.prev[bb] = prev[u];
+                        sh.bid[bb] = (double)t[u].a - t[u].w + eps; // Auction.h:250
+                        s.profits[i[u]] = t[u].w - eps;             // Auction.h:253
+                    }
+                    else
+                    {
+                        sh.col[bb] = kMissMark;
+                        atomicAdd(&sh.nmiss, 1);
+                    }
                 }
             }
         }
@@ -587,7 +690,10 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         }
         else
         {
-            int my_row = -1, my_col = -1, my_prev = -1;
+            // per column the best bid through a hash table keyed by column: insert, then a compare-and-swap
+            // argmax on the slot (highest bid, lowest row among equal bids); O(1) per bidder instead of a
+            // pass over all bidders
+            int my_row = -1, my_col = -1, my_prev = -1, my_h = -1;
             double my_bid = 0.0;
             bool win = false;
             if (tid < n)
@@ -595,24 +701,37 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
                 my_row = q[tid];
                 my_col = sh.col[tid];
                 my_bid = sh.bid[tid];
-                win = true;
-                for (int k = 0; k < n; k++)
-                    if (k != tid && sh.col[k] == my_col)
+                int h = (int)(((unsigned)my_col * 2654435761u) >> (32 - kNarrowHashBits));
+                for (;;)
+                {
+                    const int old = atomicCAS(&sh.hcol[h], -1, my_col);
+                    if (old == -1 || old == my_col)
+                        break;
+                    h = (h + 1) & (kNarrowHash - 1);
+                }
+                my_h = h;
+                int cur = *(volatile int*)&sh.hbest[h];
+                for (;;)
+                {
+                    if (cur != -1)
                     {
-                        const double ob = sh.bid[k];
-                        const int orow = q[k];
-                        if (ob > my_bid || (ob == my_bid && orow < my_row))
-                            win = false;
+                        const double ob = sh.bid[cur];
+                        if (!(my_bid > ob || (my_bid == ob && my_row < q[cur])))
+                            break;
                     }
+                    const int old = atomicCAS(&sh.hbest[h], cur, tid);
+                    if (old == cur)
+                        break;
+                    cur = old;
+                }
+            }
+            __syncthreads(); // every bid has met its column's slot
+            if (tid < n)
+            {
+                win = sh.hbest[my_h] == tid;
                 if (win)
                 {
                     my_prev = sh.prev[tid];
-                    if (my_prev >= 0)
-                    {
-                        prefetch_l1(s.cache + (long long)my_prev * kCacheK);
-                        prefetch_l1(s.cache + (long long)my_prev * kCacheK + kCacheK / 2);
-                        prefetch_l1(s.cache_hdr + my_prev);
-                    }
                     narrow_commit<kSmem, T>(s, prices_s, owner_s, my_row, my_col, my_bid, my_prev);
                     if (my_bid > sh.pmax)
                         atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax),
@@ -623,7 +742,12 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             const unsigned mask = __ballot_sync(kFullMask, push >= 0);
             if (lane == 0)
                 sh.warp_count[warp] = __popc(mask);
-            __syncthreads(); // warp_count is complete
+            __syncthreads(); // warp_count is complete, every winner has been read from the table
+            if (my_h >= 0)
+            {
+                sh.hcol[my_h] = -1;
+                sh.hbest[my_h] = -1;
+            }
             int base = 0, total = 0;
             for (int k = 0; k < kNarrowMax / 32; k++)
             {

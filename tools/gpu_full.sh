@@ -9,4 +9,4 @@ timeout 900 python bench.py > gpurun_out/bench_${TAG}.json 2> gpurun_out/bench_$
 timeout 600 python bench.py --impl reference > gpurun_out/bench_ref_${TAG}.json 2> gpurun_out/bench_ref_${TAG}.err
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/bench_under_ncu.log 2>&1
-tail -4 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cut -c1-1500 gpurun_out/bench_${TAG}.json; tail -3 gpurun_out/bench_${TAG}.err; cut -c1-600 gpurun_out/bench_ref_${TAG}.json
+tail -4 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log; cut -c1-2500 gpurun_out/bench_${TAG}.json; tail -3 gpurun_out/bench_${TAG}.err; cut -c1-600 gpurun_out/bench_ref_${TAG}.json

@@ -120,6 +120,7 @@ template <typename T> struct CsrNarrowShared
     int q[2][kThreads];      // bidder rows of this round / the next
     int bcol[kThreads];      // column bidder k bids for
     double bbid[kThreads];   // its bid
+    int bown[kThreads];      // owner of that column when the bid was made (unchanged until the commit)
     int hcol[kCsrHash];      // hash table: column, -1 empty
     int hbest[kCsrHash];     //             bidder index of the best bid so far, -1 none
     Top2<T> part[kWarpsPerBlock]; // long rows: partial results of the row's segments
@@ -133,6 +134,36 @@ template <typename T> __device__ __forceinline__ bool csr_better(const CsrNarrow
 {
     const double bx = sh.bbid[x], by = sh.bbid[y];
     return bx > by || (bx == by && q[x] < q[y]);
+}
+
+// Warp top-2 of per-lane results on the ordered bits of the doubles (narrow_kernel.cuh): five
+// redux.sync instead of five levels of 64-bit shuffles and dependent fp64 compares.  Same result as
+// top2_warp_reduce: the best is the largest v, lowest column among equals; the second best is the
+// largest of the other lanes' v and the winner's own w.  Lanes without an entry hold the start
+// value (-1e6 or -inf) and column -1.
+template <typename T> __device__ __forceinline__ void top2_warp_reduce_keys(Top2<T>& t)
+{
+    const unsigned long long kv = ordered_key(t.v);
+    const unsigned hi = (unsigned)(kv >> 32), lo = (unsigned)kv;
+    const bool has = t.j >= 0;
+    const unsigned mh = __reduce_max_sync(kFullMask, has ? hi : 0u);
+    const bool c1 = has && hi == mh;
+    const unsigned ml = __reduce_max_sync(kFullMask, c1 ? lo : 0u);
+    const bool top = c1 && lo == ml;
+    const int mj = (int)__reduce_min_sync(kFullMask, top ? (unsigned)t.j : 0xffffffffu);
+    const bool winner = top && t.j == mj;
+    const unsigned long long k2 = ordered_key(winner ? t.w : t.v); // lanes without an entry: the start value
+    const unsigned hi2 = (unsigned)(k2 >> 32), lo2 = (unsigned)k2;
+    const unsigned mh2 = __reduce_max_sync(kFullMask, hi2);
+    const unsigned ml2 = __reduce_max_sync(kFullMask, hi2 == mh2 ? lo2 : 0u);
+    const unsigned wmask = __ballot_sync(kFullMask, winner);
+    if (wmask == 0)
+        return; // no lane holds an entry: every lane keeps its (identical) empty state
+    const int src = __ffs(wmask) - 1;
+    t.a = __shfl_sync(kFullMask, t.a, src);
+    t.j = mj;
+    t.v = key_to_double(((unsigned long long)mh << 32) | ml);
+    t.w = key_to_double(((unsigned long long)mh2 << 32) | ml2);
 }
 
 // One warp: top-2 of entries [k0, k1) of a row (a segment or all of it), every lane ends with it.
@@ -154,7 +185,7 @@ __device__ __forceinline__ Top2<T> csr_scan_range(const CsrView<T>& m, const dou
         if (two)
             top2_push_stored(t, a1, p1, j1);
     }
-    top2_warp_reduce(t);
+    top2_warp_reduce_keys(t);
     return t;
 }
 
@@ -182,6 +213,7 @@ __device__ __forceinline__ void csr_post_bid(const DenseState<T>& s, const CsrVi
         s.profits[i] = t.w - eps;                   // Auction.h:253
         sh.bcol[k] = t.j;
         sh.bbid[k] = bid;
+        sh.bown[k] = s.owner[t.j]; // the load runs beside the barrier and the resolve
         if (bid > sh.pmax)
             atomicMax(reinterpret_cast<unsigned long long*>(&sh.pmax), (unsigned long long)__double_as_longlong(bid));
     }
@@ -291,7 +323,7 @@ __device__ __noinline__ long long csr_narrow_episode(const DenseState<T>& s, con
             const int row = q[tid];
             if (sh.hbest[my_h] == tid)
             {
-                const int prev = s.owner[col];
+                const int prev = sh.bown[tid];
                 s.owner[col] = row;
                 s.prices[col] = sh.bbid[tid]; // Auction.h:259
                 s.row2col[row] = col;

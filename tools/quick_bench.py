@@ -58,9 +58,9 @@ if __name__ == "__main__":
         nb = 16384 * 16384 * 4
         print(f"sweep2: zero prices min {min(a):.4f} mean {sum(a[3:])/5:.4f} ms -> {nb/min(a)/1e6:.0f} GB/s | last prices min {min(b):.4f} "
               f"mean {sum(b[3:])/5:.4f} ms -> {nb/(sum(b[3:])/5)/1e6:.0f} GB/s | solve {st['ms_solve']:.2f} ms", flush=True)
-    if "sparse" in which:
+    if "sparse" in which or "sparse20k" in which:
         import scipy.sparse as sp
-        for n, per_row in ((5000, 5000), (20000, 40), (200000, 32), (1000000, 16)):
+        for n, per_row in (((20000, 40),) if "sparse20k" in which else ((5000, 5000), (20000, 40), (200000, 32), (1000000, 16))):
             rng = np.random.default_rng(1)
             if per_row >= n:
                 a = (rng.integers(0, 1 << 24, (n, n)) + 1).astype(np.float64) / float(1 << 24)
@@ -79,6 +79,19 @@ if __name__ == "__main__":
                 print(f"sparse {n}x{n} nnz {m.nnz} {dt.__name__}: solve {st['ms_solve']:.2f} ms (upload {st['ms_upload']:.1f}, wall {wall*1e3:.1f}) "
                       f"rounds {st['rounds']} narrow {st['narrow_rounds']} bids {st['bids']} phases {st['phases']} "
                       f"objective {m[np.arange(n), r2c].sum():.6f}", flush=True)
+    if "sparse_eps" in which:
+        for n, per_row in ((20000, 40), (200000, 32)):
+            rng = np.random.default_rng(1)
+            ci = rng.integers(0, n, (n, per_row)); ci[:, 0] = rng.permutation(n); ci.sort(axis=1)
+            keep = np.ones_like(ci, bool); keep[:, 1:] = ci[:, 1:] != ci[:, :-1]
+            rp = np.concatenate([[0], np.cumsum(keep.sum(axis=1))]).astype(np.int32)
+            vals = ((rng.integers(0, 1 << 24, int(keep.sum())) + 1) / float(1 << 24)).astype(np.float32)
+            cidx = ci[keep].astype(np.int32)
+            for e0 in (0.25, 0.05, 0.01, 0.002, 0.0004):
+                for f in (4.0, 7.0, 16.0):
+                    h.solve_csr(vals, rp, cidx, n, n, eps_start=e0, eps_factor=f)
+                    st = h.last_stats
+                    print(f"sparse {n} eps0 {e0} factor {f}: {st['ms_solve']:.1f} ms rounds {st['rounds']} bids {st['bids']} phases {st['phases']}", flush=True)
     if "sq" in which:
         dense(2048, 2048); dense(4096, 4096)
     if "c4f" in which:

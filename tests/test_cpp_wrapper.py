@@ -64,3 +64,42 @@ def test_wrapper_edges_match_golden(demo, case, rowmajor):
 def test_wrapper_throws_where_the_reference_hangs(demo):
     r = subprocess.run([demo, "9", "5", "1"], capture_output=True, text=True)
     assert r.returncode == 1 and "rows <= cols" in r.stdout
+
+
+# ---- examples/lsap_b200.cpp: the reference's driver (LSAP.cpp:21-63) on the B200 path ----------------
+DRIVER = os.path.join(ROOT, "examples", "lsap_b200.cpp")
+
+
+def _compile_driver(out, extra=()):
+    from auctionalgorithm_b200 import build
+    build.build()
+    cmd = ["g++", "-std=c++11", "-O1", "-w", f"-I{ROOT}/include", *extra, DRIVER, "-o", out, f"-L{PKG}", "-lb200lsap",
+           "-lpthread", f"-Wl,-rpath,{PKG}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return out
+
+
+def test_driver_compiles_standalone_and_against_reference_headers(tmp_path):
+    exe = _compile_driver(str(tmp_path / "lsap_b200"))
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe, "8", "12"], capture_output=True, text=True)
+        assert r.returncode == 1 and "no CUDA device" in r.stdout
+    if os.path.exists(os.path.join(REF, "AuctionAlgorithm", "Auction.h")):
+        _compile_driver(str(tmp_path / "lsap_b200_eigen"), ("-DWITH_REFERENCE_EIGEN", f"-I{REF}", f"-I{REF}/external"))
+
+
+@pytest.mark.gpu
+def test_driver_prints_the_reference_lines_and_four_equal_objectives(tmp_path):
+    exe = _compile_driver(str(tmp_path / "lsap_b200"))
+    r = subprocess.run([exe, "300", "300", "7"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = r.stdout.strip().splitlines()
+    assert len(lines) == 8
+    assert all(l.startswith("command  <solution = Auction") and l.rstrip().endswith("us") for l in lines[0::2])
+    objs = [float(l.split(":")[1]) for l in lines[1::2]]
+    assert all(l.startswith("objective function value:") for l in lines[1::2])
+    # dense, sparse, "MT" dense, "MT" sparse: the same optimum (the matrix has no zero, so the sparse
+    # matrix holds every coefficient, as in LSAP.cpp:36-38)
+    assert max(objs) - min(objs) <= 300 * (1e-5 / 300) and 290 < objs[0] <= 300

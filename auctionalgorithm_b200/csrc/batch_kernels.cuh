@@ -356,6 +356,310 @@ __global__ void __launch_bounds__(32, kWarpsPerSm) k_auction_batch_stream(BatchP
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Filtered form (the default for cols % 4 == 0): the same Gauss-Seidel bids in the same order, but a
+// bid no longer evaluates every column in fp64.  findForward (Auction.h:124-152) needs three exact
+// things: the best column (lowest column among equals), its coefficient, and the second-best value.
+// A single-precision pass finds the three largest a_ij - (float)p_j of the row with the column number
+// carried in the six low mantissa bits of each value (top-3 by value only: five FMNMX per element, no
+// index selects); the two leaders are then evaluated exactly in fp64, and the result is accepted only
+// if the third key, raised by a bound on everything the fp32 pass may have lost (key truncation 2^-17,
+// the subtraction's rounding 2^-24, the price's rounding 2^-24 * max price), still lies strictly below
+// the exact second-best value.  Otherwise (about one bid in a thousand on uniform data; always when a
+// row has fewer than two edges) the group re-scans the row with the exact fp64 top-2 of the other
+// kernels, so every bid is the reference's bid whatever the data — the filter only decides how much
+// work it takes.  Coefficients are assumed finite (the reference's contract is [0, 1], LSAP.cpp:25).
+//
+// Layout: 2 lanes per problem, 16 problems per warp; lane gl of a group owns the float4 chunks
+// 2m + gl of a row (columns 8m + 4gl .. +3), so a pair reads one 32-byte sector per instruction.
+// Prices (fp64 and their fp32 roundings), column owners and the bidding row live in shared memory
+// (888 bytes per 32x48 problem): a bid updates one entry of each with a store instead of a
+// select chain over registers.  A warp owns a contiguous slice of the batch and hands the next
+// problem to whichever group finishes (the bid count of a 32x48 problem ranges from 32 to 200+; a
+// warp that waited for its slowest group would idle 27 % of its lanes).
+// ---------------------------------------------------------------------------------------------
+// key of "no edge here": finite (the column bits must not turn it into a NaN), its six low bits clear
+// (an untouched accumulator then names column 0, a valid index into the shared arrays)
+#define B200LSAP_FILTER_NONE __uint_as_float(0xFF61B1C0u) /* -3.0e38f */
+
+struct Top3f
+{
+    float m1, m2, m3;
+};
+
+__device__ __forceinline__ void top3_push(Top3f& t, float x)
+{
+    t.m3 = fmaxf(t.m3, fminf(t.m2, x));
+    t.m2 = fmaxf(t.m2, fminf(t.m1, x));
+    t.m1 = fmaxf(t.m1, x);
+}
+
+// both sorted; result = the three largest of the six
+__device__ __forceinline__ void top3_merge(Top3f& t, const Top3f& o)
+{
+    const float x = fminf(t.m1, o.m1), y = fmaxf(t.m2, o.m2);
+    t.m3 = fmaxf(fmaxf(fminf(x, y), t.m3), o.m3);
+    t.m2 = fmaxf(x, y);
+    t.m1 = fmaxf(t.m1, o.m1);
+}
+
+__device__ __forceinline__ float filter_key(float a, float p32, int col)
+{
+    const float d = a != 0.f ? a - p32 : B200LSAP_FILTER_NONE;
+    return __uint_as_float((__float_as_uint(d) & ~63u) | (unsigned)col);
+}
+
+// stride (floats) of the per-problem fp32 arrays: >= 8 kM and = 8 mod 16, so the four problems of a
+// quarter warp read disjoint 8-bank windows with 128-bit loads
+__host__ __device__ inline int batch_filter_stride(int kM)
+{
+    int s = 8 * kM;
+    while ((s & 15) != 8)
+        s += 8;
+    return s;
+}
+__host__ __device__ inline size_t batch_filter_warp_bytes(int kM)
+{
+    return (size_t)16 * (2 * batch_filter_stride(kM) * 4 + 8 * kM * 8 + 8 * kM);
+}
+
+template <int kM, int kWarps, int kCtasPerSm>
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filter(BatchParams P)
+{
+    extern __shared__ __align__(16) unsigned char batch_smem[];
+    constexpr int kC8 = 8 * kM;
+    const int s32 = batch_filter_stride(kM);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 1, gl = lane & 1;
+    unsigned char* wb = batch_smem + warp * batch_filter_warp_bytes(kM);
+    float* p32 = reinterpret_cast<float*>(wb) + g * s32;                       // (float)price[col]
+    float* arow = reinterpret_cast<float*>(wb) + 16 * s32 + g * s32;           // the bidding row
+    double* p64 = reinterpret_cast<double*>(wb + 2 * 16 * s32 * 4) + g * kC8;  // price[col] (Auction.h:58)
+    signed char* own = reinterpret_cast<signed char*>(wb + 2 * 16 * s32 * 4 + 16 * kC8 * 8) + g * kC8;
+    const int n = P.rows * P.cols;
+    const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
+    const unsigned lanes_before = (1u << lane) - 1u;
+    const unsigned pair = 3u << (2 * g);
+
+    // this warp's slice of the batch
+    const long long W = (long long)gridDim.x * kWarps, w = (long long)warp * gridDim.x + blockIdx.x;
+    long long next = P.batch / W * w + min(w, P.batch % W);
+    const long long end = next + P.batch / W + (w < P.batch % W ? 1 : 0);
+
+    long long pb = -1;              // the group's problem
+    const float* __restrict__ A = P.a;
+    unsigned unassigned = 0, todo = 0;
+    int bids = 0, fail = 0;
+    bool done = false;
+    float pmax = 0.f;               // upper bound of the problem's prices
+    float4 nx[kM];                  // prefetched row nx_i
+    int nx_i = -1;
+
+    while (true)
+    {
+        const bool need = unassigned == 0 && !done;
+        const unsigned nm = __ballot_sync(kFullMask, need);
+        if (nm)
+        {
+            if (need)
+            {
+                if (pb >= 0)
+                {
+                    // row -> column from the owners, through the row buffer, then 32-bit coalesced stores
+                    int* r2c = reinterpret_cast<int*>(arow);
+                    for (int r = gl; r < P.rows; r += 2)
+                        r2c[r] = -1;
+                    __syncwarp(pair);
+#pragma unroll
+                    for (int m = 0; m < kM; m++)
+#pragma unroll
+                        for (int e = 0; e < 4; e++)
+                        {
+                            const int c = 8 * m + 4 * gl + e;
+                            const int o = own[c];
+                            if (o >= 0)
+                                r2c[o] = c;
+                        }
+                    __syncwarp(pair);
+                    int* out = P.row2col + pb * P.rows;
+                    for (int r = gl; r < P.rows; r += 2)
+                        out[r] = r2c[r];
+                    if (fail && gl == 0)
+                        *P.status = fail;
+                    __syncwarp(pair);
+                }
+                const long long np = next + (__popc(nm & lanes_before) >> 1);
+                if (np < end)
+                {
+                    pb = np;
+                    A = P.a + pb * n;
+#pragma unroll
+                    for (int m = 0; m < kM; m++)
+                    {
+                        const int c = 8 * m + 4 * gl;
+                        *reinterpret_cast<float4*>(p32 + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+                        *reinterpret_cast<double2*>(p64 + c) = make_double2(0.0, 0.0);
+                        *reinterpret_cast<double2*>(p64 + c + 2) = make_double2(0.0, 0.0);
+                        *reinterpret_cast<int*>(own + c) = -1;
+                        nx[m] = (m < kM - 1 || c < P.cols) ? __ldg(reinterpret_cast<const float4*>(A + c))
+                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    nx_i = 0;
+                    unassigned = all_rows;
+                    todo = 0;
+                    bids = 0;
+                    fail = 0;
+                    pmax = 0.f;
+                }
+                else
+                {
+                    pb = -1;
+                    done = true;
+                }
+            }
+            next += __popc(nm) >> 1;
+            __syncwarp();
+            if (__all_sync(kFullMask, done))
+                break;
+        }
+
+        if (todo == 0)
+            todo = unassigned; // next forward sweep (Auction.h:66-68, :220): rows in increasing order
+        const bool act = todo != 0;
+        const int i = act ? __ffs(todo) - 1 : 0;
+        todo &= todo - 1;
+        float4 a[kM];
+        if (act && nx_i == i)
+        {
+#pragma unroll
+            for (int m = 0; m < kM; m++)
+                a[m] = nx[m];
+        }
+        else
+        {
+            const float* row = A + i * P.cols;
+#pragma unroll
+            for (int m = 0; m < kM; m++)
+            {
+                const int c = 8 * m + 4 * gl;
+                a[m] = (act && (m < kM - 1 || c < P.cols)) ? __ldg(reinterpret_cast<const float4*>(row + c))
+                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        if (todo != 0)
+        {
+            const int i2 = __ffs(todo) - 1;
+            const float* row2 = A + i2 * P.cols;
+#pragma unroll
+            for (int m = 0; m < kM; m++)
+            {
+                const int c = 8 * m + 4 * gl;
+                nx[m] = (m < kM - 1 || c < P.cols) ? __ldg(reinterpret_cast<const float4*>(row2 + c))
+                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            nx_i = i2;
+        }
+        else
+            nx_i = -1;
+
+        // single-precision pass: the three largest keys of the row
+        Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE};
+#pragma unroll
+        for (int m = 0; m < kM; m++)
+        {
+            const int c = 8 * m + 4 * gl;
+            *reinterpret_cast<float4*>(arow + c) = a[m];
+            const float4 pp = *reinterpret_cast<const float4*>(p32 + c);
+            top3_push(t3, filter_key(a[m].x, pp.x, c));
+            top3_push(t3, filter_key(a[m].y, pp.y, c + 1));
+            top3_push(t3, filter_key(a[m].z, pp.z, c + 2));
+            top3_push(t3, filter_key(a[m].w, pp.w, c + 3));
+        }
+        {
+            Top3f o;
+            o.m1 = __shfl_xor_sync(kFullMask, t3.m1, 1);
+            o.m2 = __shfl_xor_sync(kFullMask, t3.m2, 1);
+            o.m3 = __shfl_xor_sync(kFullMask, t3.m3, 1);
+            top3_merge(t3, o);
+        }
+        __syncwarp(); // the row is in shared memory
+
+        // the two leaders, exactly (Auction.h:131-150: strict '>' keeps the lowest column among equals)
+        const int c1 = __float_as_uint(t3.m1) & 63, c2 = __float_as_uint(t3.m2) & 63;
+        const float a1 = arow[c1], a2 = arow[c2];
+        const double d1 = widen_exact(a1) - p64[c1], d2 = widen_exact(a2) - p64[c2];
+        const bool first = d1 > d2 || (d1 == d2 && c1 < c2);
+        int j = first ? c1 : c2;
+        float aj = first ? a1 : a2;
+        double wv = first ? d2 : d1;
+        // nothing else can reach the second-best value
+        const float k3 = t3.m3;
+        const float bound = k3 + (fabsf(k3) * 3.0517578125e-5f + pmax * 4.76837158203125e-7f + 1e-30f);
+        const bool fast = t3.m2 > -5.0e5f && wv > (double)bound;
+        if (__any_sync(kFullMask, act && !fast))
+        {
+            // exact scan of the whole row (the other kernels' top-2), for the groups that need it
+            Top2<float> t = top2_empty<float>();
+#pragma unroll
+            for (int m = 0; m < kM; m++)
+            {
+                const int c = 8 * m + 4 * gl;
+                if (m < kM - 1 || c < P.cols)
+                {
+                    top2_push(t, a[m].x, p64[c], c);
+                    top2_push(t, a[m].y, p64[c + 1], c + 1);
+                    top2_push(t, a[m].z, p64[c + 2], c + 2);
+                    top2_push(t, a[m].w, p64[c + 3], c + 3);
+                }
+            }
+            const Top2<float> o = top2_shfl_xor(t, 1);
+            top2_merge(t, o);
+            if (!fast)
+            {
+                j = t.j;
+                aj = t.a;
+                wv = t.w;
+            }
+        }
+        const bool ok = act && j >= 0;
+        const double bid = (double)aj - wv + P.eps; // Auction.h:250
+        // lambda = 0 <= bid always holds here (Auction.h:257): assign, evict the owner
+        const int prev = ok ? (int)own[j] : -1;
+        __syncwarp();
+        if (ok)
+        {
+            const float b32 = __double2float_rn(bid);
+            if (gl == 0)
+            {
+                own[j] = (signed char)i;
+                p64[j] = bid;
+                p32[j] = b32;
+            }
+            pmax = fmaxf(pmax, b32);
+            unassigned &= ~(1u << i);
+            if (prev >= 0)
+            {
+                unassigned |= 1u << prev; // Auction.h:270
+                if (prev > i)
+                    todo |= 1u << prev; // unlocked ahead of the sweep position: visited in this sweep
+            }
+            if (++bids > P.max_bids)
+            {
+                fail = 3;
+                unassigned = 0;
+                todo = 0;
+            }
+        }
+        else if (act)
+        {
+            fail = 2; // a row without an edge: the reference would never return
+            unassigned = 0;
+            todo = 0;
+        }
+        __syncwarp();
+    }
+}
+
 // Column-major problems (Eigen's default) -> row-major problems, one pass over the batch.
 __global__ void __launch_bounds__(256) k_batch_to_row_major(const float* __restrict__ in, float* __restrict__ out,
                                                             long long batch, int rows, int cols)

@@ -995,8 +995,29 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     // SM the streaming kernel is compiled for (developer A/B knobs)
     static const bool smem_mode = getenv("B200LSAP_BATCH_SMEM") && atoi(getenv("B200LSAP_BATCH_SMEM")) != 0;
     static const int warps_mode = getenv("B200LSAP_BATCH_WARPS") ? atoi(getenv("B200LSAP_BATCH_WARPS")) : 32;
+    // B200LSAP_BATCH_FILTER=0: without the single-precision filter (k_auction_batch_stream)
+    static const bool filter_mode = !(getenv("B200LSAP_BATCH_FILTER") && atoi(getenv("B200LSAP_BATCH_FILTER")) == 0);
     CU(cudaEventRecord(h->ev[1], h->stream));
-    if (!smem_mode)
+    if (!smem_mode && filter_mode && cols % 4 == 0 && ((uintptr_t)a_dev_row_major & 15) == 0)
+    {
+        // 16 problems per warp, four warps per CTA, one resident wave; a warp takes a slice of the batch
+        constexpr int kFW = 4, kFC = 4;
+#define B200LSAP_FILTER(M) k_auction_batch_filter<M, kFW, kFC>
+        static const BatchKernel kf[8] = {B200LSAP_FILTER(1), B200LSAP_FILTER(2), B200LSAP_FILTER(3),
+                                          B200LSAP_FILTER(4), B200LSAP_FILTER(5), B200LSAP_FILTER(6),
+                                          B200LSAP_FILTER(7), B200LSAP_FILTER(8)};
+        const int kM = (cols + 7) / 8;
+        const BatchKernel fk = kf[kM - 1];
+        const size_t fsmem = kFW * batch_filter_warp_bytes(kM);
+        CU(cudaFuncSetAttribute(fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+        int fper_sm = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fper_sm, fk, kFW * 32, fsmem));
+        if (fper_sm < 1)
+            return fail(h, B200LSAP_ERR_CUDA, "k_auction_batch_filter does not fit on an SM");
+        int64_t fgrid = std::min<int64_t>((batch + 16 * kFW - 1) / (16 * kFW), (int64_t)fper_sm * h->num_sms);
+        fk<<<(int)std::max<int64_t>(fgrid, 1), kFW * 32, fsmem, h->stream>>>(P);
+    }
+    else if (!smem_mode)
     {
         // lanes per problem: 8 (columns per lane <= 8) or 4 (columns per lane <= 16)
         static const int lanes_mode = getenv("B200LSAP_BATCH_LANES") ? atoi(getenv("B200LSAP_BATCH_LANES")) : 4;

@@ -361,22 +361,27 @@ __global__ void __launch_bounds__(32, kWarpsPerSm) k_auction_batch_stream(BatchP
 // bid no longer evaluates every column in fp64.  findForward (Auction.h:124-152) needs three exact
 // things: the best column (lowest column among equals), its coefficient, and the second-best value.
 // A single-precision pass finds the three largest a_ij - (float)p_j of the row with the column number
-// carried in the six low mantissa bits of each value (top-3 by value only: five FMNMX per element, no
-// index selects); the two leaders are then evaluated exactly in fp64, and the result is accepted only
-// if the third key, raised by a bound on everything the fp32 pass may have lost (key truncation 2^-17,
-// the subtraction's rounding 2^-24, the price's rounding 2^-24 * max price), still lies strictly below
-// the exact second-best value.  Otherwise (about one bid in a thousand on uniform data; always when a
-// row has fewer than two edges) the group re-scans the row with the exact fp64 top-2 of the other
-// kernels, so every bid is the reference's bid whatever the data — the filter only decides how much
-// work it takes.  Coefficients are assumed finite (the reference's contract is [0, 1], LSAP.cpp:25).
+// carried in the six low mantissa bits of each value (top-3 by value only, two elements at a time:
+// four FMNMX/FMNMX3 per element, no index selects); the two leaders are then evaluated exactly in fp64,
+// and the result is accepted only if the third key, raised by a bound on everything the fp32 pass may
+// have lost (key truncation 2^-17, the subtraction's rounding 2^-24, the price's rounding 2^-24 * max
+// price), still lies strictly below the exact second-best value.  Otherwise (about one bid in a
+// thousand on uniform data; always when a row has fewer than two edges) the group re-scans the row
+// with the exact fp64 top-2 of the other kernels, so every bid is the reference's bid whatever the
+// data — the filter only decides how much work it takes.  "a_ij == 0 is no edge" (Auction.h:134) costs
+// two instructions per element, so the pass starts without it and a zero among the two leaders sends the
+// bid to the exact scan and switches the warp to the zero-aware pass for the rest of its slice.
+// Coefficients are assumed finite (the reference's contract is [0, 1], LSAP.cpp:25).
 //
 // Layout: 2 lanes per problem, 16 problems per warp; lane gl of a group owns the float4 chunks
 // 2m + gl of a row (columns 8m + 4gl .. +3), so a pair reads one 32-byte sector per instruction.
-// Prices (fp64 and their fp32 roundings), column owners and the bidding row live in shared memory
-// (888 bytes per 32x48 problem): a bid updates one entry of each with a store instead of a
-// select chain over registers.  A warp owns a contiguous slice of the batch and hands the next
-// problem to whichever group finishes (the bid count of a 32x48 problem ranges from 32 to 200+; a
-// warp that waited for its slowest group would idle 27 % of its lanes).
+// Prices (fp64 and their fp32 roundings), column owners, the assignment and two row buffers live in
+// shared memory (1136 bytes per 32x48 problem): a bid updates one entry of each with a store instead
+// of a select chain over registers, and the next row of the sweep arrives by cp.async while the current
+// one bids.  A warp owns a contiguous slice of the batch and hands the next problems to the groups that
+// have finished (the bid count of a 32x48 problem ranges from 32 to 200+; a warp that waited for its
+// slowest group would idle 27 % of its lanes); it does so when two groups are waiting, so the divergent
+// hand-over code runs half as often.
 // ---------------------------------------------------------------------------------------------
 // key of "no edge here": finite (the column bits must not turn it into a NaN), its six low bits clear
 // (an untouched accumulator then names column 0, a valid index into the shared arrays)
@@ -387,11 +392,14 @@ struct Top3f
     float m1, m2, m3;
 };
 
-__device__ __forceinline__ void top3_push(Top3f& t, float x)
+// two new elements into the sorted triple
+__device__ __forceinline__ void top3_push2(Top3f& t, float x, float y)
 {
-    t.m3 = fmaxf(t.m3, fminf(t.m2, x));
-    t.m2 = fmaxf(t.m2, fminf(t.m1, x));
-    t.m1 = fmaxf(t.m1, x);
+    const float hi = fmaxf(x, y), lo = fminf(x, y);
+    const float a = fminf(t.m1, hi), b = fminf(t.m2, hi), c = fminf(t.m1, lo);
+    t.m3 = fmaxf(fmaxf(t.m3, b), c);
+    t.m2 = fmaxf(fmaxf(t.m2, a), lo);
+    t.m1 = fmaxf(t.m1, hi);
 }
 
 // both sorted; result = the three largest of the six
@@ -403,10 +411,26 @@ __device__ __forceinline__ void top3_merge(Top3f& t, const Top3f& o)
     t.m1 = fmaxf(t.m1, o.m1);
 }
 
-__device__ __forceinline__ float filter_key(float a, float p32, int col)
+template <bool kZeroAware> __device__ __forceinline__ float filter_key(float a, float p32, int col)
 {
-    const float d = a != 0.f ? a - p32 : B200LSAP_FILTER_NONE;
+    const float d = (!kZeroAware || a != 0.f) ? a - p32 : B200LSAP_FILTER_NONE;
     return __uint_as_float((__float_as_uint(d) & ~63u) | (unsigned)col);
+}
+
+template <bool kZeroAware, int kM>
+__device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, const float* __restrict__ p32, int gl)
+{
+    Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE};
+#pragma unroll
+    for (int m = 0; m < kM; m++)
+    {
+        const int c = 8 * m + 4 * gl;
+        const float4 av = *reinterpret_cast<const float4*>(row + c);
+        const float4 pp = *reinterpret_cast<const float4*>(p32 + c);
+        top3_push2(t3, filter_key<kZeroAware>(av.x, pp.x, c), filter_key<kZeroAware>(av.y, pp.y, c + 1));
+        top3_push2(t3, filter_key<kZeroAware>(av.z, pp.z, c + 2), filter_key<kZeroAware>(av.w, pp.w, c + 3));
+    }
+    return t3;
 }
 
 // stride (floats) of the per-problem fp32 arrays: >= 8 kM and = 8 mod 16, so the four problems of a
@@ -418,9 +442,22 @@ __host__ __device__ inline int batch_filter_stride(int kM)
         s += 8;
     return s;
 }
+// per warp: fp32 prices + two row buffers (3 x 16 x stride floats), fp64 prices, owners, assignment
 __host__ __device__ inline size_t batch_filter_warp_bytes(int kM)
 {
-    return (size_t)16 * (2 * batch_filter_stride(kM) * 4 + 8 * kM * 8 + 8 * kM);
+    return (size_t)16 * (3 * batch_filter_stride(kM) * 4 + 8 * kM * 8 + 8 * kM + 32);
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending> __device__ __forceinline__ void cp_async_wait()
+{
+    asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
 }
 
 template <int kM, int kWarps, int kCtasPerSm>
@@ -433,13 +470,22 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     const int g = lane >> 1, gl = lane & 1;
     unsigned char* wb = batch_smem + warp * batch_filter_warp_bytes(kM);
     float* p32 = reinterpret_cast<float*>(wb) + g * s32;                       // (float)price[col]
-    float* arow = reinterpret_cast<float*>(wb) + 16 * s32 + g * s32;           // the bidding row
-    double* p64 = reinterpret_cast<double*>(wb + 2 * 16 * s32 * 4) + g * kC8;  // price[col] (Auction.h:58)
-    signed char* own = reinterpret_cast<signed char*>(wb + 2 * 16 * s32 * 4 + 16 * kC8 * 8) + g * kC8;
+    float* rowbuf = reinterpret_cast<float*>(wb) + 16 * s32 + g * s32;         // + cur * 16 * s32: the bidding row
+    double* p64 = reinterpret_cast<double*>(wb + 3 * 16 * s32 * 4) + g * kC8;  // price[col] (Auction.h:58)
+    signed char* own = reinterpret_cast<signed char*>(wb + 3 * 16 * s32 * 4 + 16 * kC8 * 8) + g * kC8;
+    signed char* mc = reinterpret_cast<signed char*>(wb + 3 * 16 * s32 * 4 + 16 * kC8 * 9) + g * 32; // row -> column
     const int n = P.rows * P.cols;
     const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
     const unsigned lanes_before = (1u << lane) - 1u;
     const unsigned pair = 3u << (2 * g);
+    // this lane's last chunk lies beyond the row when cols % 8 == 4: never loaded, reads as "no edge"
+    const bool last_chunk = 8 * (kM - 1) + 4 * gl < P.cols;
+    if (!last_chunk)
+    {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(rowbuf + 8 * (kM - 1) + 4 * gl) = z;
+        *reinterpret_cast<float4*>(rowbuf + 16 * s32 + 8 * (kM - 1) + 4 * gl) = z;
+    }
 
     // this warp's slice of the batch
     const long long W = (long long)gridDim.x * kWarps, w = (long long)warp * gridDim.x + blockIdx.x;
@@ -451,60 +497,54 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     unsigned unassigned = 0, todo = 0;
     int bids = 0, fail = 0;
     bool done = false;
+    bool zero_aware = false;        // warp-uniform, sticky
     float pmax = 0.f;               // upper bound of the problem's prices
-    float4 nx[kM];                  // prefetched row nx_i
-    int nx_i = -1;
+    int cur = 0;                    // row buffer of the current bid; the other one receives the prefetch
+    int pf_i = -1;                  // row the other buffer holds (or will, once its cp.async lands)
 
     while (true)
     {
         const bool need = unassigned == 0 && !done;
         const unsigned nm = __ballot_sync(kFullMask, need);
-        if (nm)
+        const unsigned am = __ballot_sync(kFullMask, unassigned != 0);
+        if (__popc(nm) >= 4 || (nm != 0 && am == 0))
         {
             if (need)
             {
                 if (pb >= 0)
                 {
-                    // row -> column from the owners, through the row buffer, then 32-bit coalesced stores
-                    int* r2c = reinterpret_cast<int*>(arow);
-                    for (int r = gl; r < P.rows; r += 2)
-                        r2c[r] = -1;
-                    __syncwarp(pair);
+                    // rows 16 gl .. 16 gl + 15 of the finished problem
+                    const int4 q = *reinterpret_cast<const int4*>(mc + 16 * gl);
+                    const int qq[4] = {q.x, q.y, q.z, q.w};
+                    int* out = P.row2col + pb * P.rows + 16 * gl;
 #pragma unroll
-                    for (int m = 0; m < kM; m++)
-#pragma unroll
-                        for (int e = 0; e < 4; e++)
-                        {
-                            const int c = 8 * m + 4 * gl + e;
-                            const int o = own[c];
-                            if (o >= 0)
-                                r2c[o] = c;
-                        }
-                    __syncwarp(pair);
-                    int* out = P.row2col + pb * P.rows;
-                    for (int r = gl; r < P.rows; r += 2)
-                        out[r] = r2c[r];
+                    for (int k = 0; k < 16; k++)
+                        if (16 * gl + k < P.rows)
+                            out[k] = (int)(signed char)(qq[k >> 2] >> (8 * (k & 3)));
                     if (fail && gl == 0)
                         *P.status = fail;
-                    __syncwarp(pair);
                 }
                 const long long np = next + (__popc(nm & lanes_before) >> 1);
                 if (np < end)
                 {
                     pb = np;
                     A = P.a + pb * n;
+                    float* nb = rowbuf + (cur ^ 1) * 16 * s32;
 #pragma unroll
                     for (int m = 0; m < kM; m++)
                     {
                         const int c = 8 * m + 4 * gl;
-                        *reinterpret_cast<float4*>(p32 + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+                        // a column beyond the row is priced out of the single-precision pass
+                        const float p0 = (m < kM - 1 || last_chunk) ? 0.f : 3.0e38f;
+                        *reinterpret_cast<float4*>(p32 + c) = make_float4(p0, p0, p0, p0);
                         *reinterpret_cast<double2*>(p64 + c) = make_double2(0.0, 0.0);
                         *reinterpret_cast<double2*>(p64 + c + 2) = make_double2(0.0, 0.0);
                         *reinterpret_cast<int*>(own + c) = -1;
-                        nx[m] = (m < kM - 1 || c < P.cols) ? __ldg(reinterpret_cast<const float4*>(A + c))
-                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m < kM - 1 || last_chunk)
+                            cp_async16(nb + c, A + c);
                     }
-                    nx_i = 0;
+                    *reinterpret_cast<int4*>(mc + 16 * gl) = make_int4(-1, -1, -1, -1);
+                    pf_i = 0;
                     unassigned = all_rows;
                     todo = 0;
                     bids = 0;
@@ -528,53 +568,41 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         const bool act = todo != 0;
         const int i = act ? __ffs(todo) - 1 : 0;
         todo &= todo - 1;
-        float4 a[kM];
-        if (act && nx_i == i)
+        // the row of this bid: normally the one prefetched during the previous bid
+        if (act)
         {
-#pragma unroll
-            for (int m = 0; m < kM; m++)
-                a[m] = nx[m];
-        }
-        else
-        {
-            const float* row = A + i * P.cols;
-#pragma unroll
-            for (int m = 0; m < kM; m++)
+            cur ^= 1;
+            if (pf_i != i)
             {
-                const int c = 8 * m + 4 * gl;
-                a[m] = (act && (m < kM - 1 || c < P.cols)) ? __ldg(reinterpret_cast<const float4*>(row + c))
-                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float* row = A + i * P.cols;
+                float* cb = rowbuf + cur * 16 * s32;
+#pragma unroll
+                for (int m = 0; m < kM; m++)
+                    if (m < kM - 1 || last_chunk)
+                        cp_async16(cb + 8 * m + 4 * gl, row + 8 * m + 4 * gl);
             }
         }
+        cp_async_commit();
+        // the next row of this sweep, if the sweep goes on (an eviction ahead of it is rare and only
+        // costs the direct load above)
         if (todo != 0)
         {
-            const int i2 = __ffs(todo) - 1;
-            const float* row2 = A + i2 * P.cols;
+            pf_i = __ffs(todo) - 1;
+            const float* row2 = A + pf_i * P.cols;
+            float* nb = rowbuf + (cur ^ 1) * 16 * s32;
 #pragma unroll
             for (int m = 0; m < kM; m++)
-            {
-                const int c = 8 * m + 4 * gl;
-                nx[m] = (m < kM - 1 || c < P.cols) ? __ldg(reinterpret_cast<const float4*>(row2 + c))
-                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            nx_i = i2;
+                if (m < kM - 1 || last_chunk)
+                    cp_async16(nb + 8 * m + 4 * gl, row2 + 8 * m + 4 * gl);
         }
         else
-            nx_i = -1;
+            pf_i = -1;
+        cp_async_commit();
+        cp_async_wait<1>();
+        const float* row = rowbuf + cur * 16 * s32;
 
-        // single-precision pass: the three largest keys of the row
-        Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE};
-#pragma unroll
-        for (int m = 0; m < kM; m++)
-        {
-            const int c = 8 * m + 4 * gl;
-            *reinterpret_cast<float4*>(arow + c) = a[m];
-            const float4 pp = *reinterpret_cast<const float4*>(p32 + c);
-            top3_push(t3, filter_key(a[m].x, pp.x, c));
-            top3_push(t3, filter_key(a[m].y, pp.y, c + 1));
-            top3_push(t3, filter_key(a[m].z, pp.z, c + 2));
-            top3_push(t3, filter_key(a[m].w, pp.w, c + 3));
-        }
+        // single-precision pass over this lane's chunks (its own copies: no synchronisation needed yet)
+        Top3f t3 = zero_aware ? filter_pass<true, kM>(row, p32, gl) : filter_pass<false, kM>(row, p32, gl);
         {
             Top3f o;
             o.m1 = __shfl_xor_sync(kFullMask, t3.m1, 1);
@@ -582,11 +610,11 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             o.m3 = __shfl_xor_sync(kFullMask, t3.m3, 1);
             top3_merge(t3, o);
         }
-        __syncwarp(); // the row is in shared memory
+        __syncwarp(); // the partner's half of the row has landed too
 
         // the two leaders, exactly (Auction.h:131-150: strict '>' keeps the lowest column among equals)
         const int c1 = __float_as_uint(t3.m1) & 63, c2 = __float_as_uint(t3.m2) & 63;
-        const float a1 = arow[c1], a2 = arow[c2];
+        const float a1 = row[c1], a2 = row[c2];
         const double d1 = widen_exact(a1) - p64[c1], d2 = widen_exact(a2) - p64[c2];
         const bool first = d1 > d2 || (d1 == d2 && c1 < c2);
         int j = first ? c1 : c2;
@@ -595,21 +623,25 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         // nothing else can reach the second-best value
         const float k3 = t3.m3;
         const float bound = k3 + (fabsf(k3) * 3.0517578125e-5f + pmax * 4.76837158203125e-7f + 1e-30f);
-        const bool fast = t3.m2 > -5.0e5f && wv > (double)bound;
+        const bool nonzero = a1 != 0.f && a2 != 0.f;
+        const bool fast = t3.m2 > -5.0e5f && wv > (double)bound && nonzero;
         if (__any_sync(kFullMask, act && !fast))
         {
+            if (__any_sync(kFullMask, act && !nonzero))
+                zero_aware = true;
             // exact scan of the whole row (the other kernels' top-2), for the groups that need it
             Top2<float> t = top2_empty<float>();
 #pragma unroll
             for (int m = 0; m < kM; m++)
             {
                 const int c = 8 * m + 4 * gl;
-                if (m < kM - 1 || c < P.cols)
+                if (m < kM - 1 || last_chunk)
                 {
-                    top2_push(t, a[m].x, p64[c], c);
-                    top2_push(t, a[m].y, p64[c + 1], c + 1);
-                    top2_push(t, a[m].z, p64[c + 2], c + 2);
-                    top2_push(t, a[m].w, p64[c + 3], c + 3);
+                    const float4 av = *reinterpret_cast<const float4*>(row + c);
+                    top2_push(t, av.x, p64[c], c);
+                    top2_push(t, av.y, p64[c + 1], c + 1);
+                    top2_push(t, av.z, p64[c + 2], c + 2);
+                    top2_push(t, av.w, p64[c + 3], c + 3);
                 }
             }
             const Top2<float> o = top2_shfl_xor(t, 1);
@@ -632,6 +664,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             if (gl == 0)
             {
                 own[j] = (signed char)i;
+                mc[i] = (signed char)j;
                 p64[j] = bid;
                 p32[j] = b32;
             }
@@ -658,7 +691,9 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         }
         __syncwarp();
     }
+    cp_async_wait<0>();
 }
+
 
 // Column-major problems (Eigen's default) -> row-major problems, one pass over the batch.
 __global__ void __launch_bounds__(256) k_batch_to_row_major(const float* __restrict__ in, float* __restrict__ out,

@@ -460,7 +460,8 @@ template <int kPending> __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
 }
 
-template <int kM, int kWarps, int kCtasPerSm>
+// kWhole: cols % 8 == 0, every lane's last chunk lies inside the row (no predicate around its copies)
+template <int kM, bool kWhole, int kWarps, int kCtasPerSm>
 __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filter(BatchParams P)
 {
     extern __shared__ __align__(16) unsigned char batch_smem[];
@@ -479,7 +480,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     const unsigned lanes_before = (1u << lane) - 1u;
     const unsigned pair = 3u << (2 * g);
     // this lane's last chunk lies beyond the row when cols % 8 == 4: never loaded, reads as "no edge"
-    const bool last_chunk = 8 * (kM - 1) + 4 * gl < P.cols;
+    const bool last_chunk = kWhole || 8 * (kM - 1) + 4 * gl < P.cols;
     if (!last_chunk)
     {
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -574,6 +575,9 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             cur ^= 1;
             if (pf_i != i)
             {
+                // this buffer may still be receiving the row that was prefetched instead (issued a bid ago):
+                // it must have landed before the right row is copied over it
+                cp_async_wait<0>();
                 const float* row = A + i * P.cols;
                 float* cb = rowbuf + cur * 16 * s32;
 #pragma unroll
@@ -615,7 +619,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         // the two leaders, exactly (Auction.h:131-150: strict '>' keeps the lowest column among equals)
         const int c1 = __float_as_uint(t3.m1) & 63, c2 = __float_as_uint(t3.m2) & 63;
         const float a1 = row[c1], a2 = row[c2];
-        const double d1 = widen_exact(a1) - p64[c1], d2 = widen_exact(a2) - p64[c2];
+        const double d1 = (double)a1 - p64[c1], d2 = (double)a2 - p64[c2]; // two conversions per bid: no XU pressure
         const bool first = d1 > d2 || (d1 == d2 && c1 < c2);
         int j = first ? c1 : c2;
         float aj = first ? a1 : a2;

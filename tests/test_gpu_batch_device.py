@@ -47,6 +47,92 @@ def test_batch_with_zeros_and_ties(handle, oracle_lib):
     assert np.array_equal(handle.solve_batch(a), ref)
 
 
+# ---- the filtered kernel (cols % 4 == 0): every way its single-precision pass can be wrong-footed -------------
+@pytest.mark.parametrize("shape", [(1, 4), (3, 4), (4, 4), (8, 8), (7, 12), (20, 20), (32, 36), (32, 44), (30, 60),
+                                   (32, 48), (16, 56), (2, 64)])
+def test_filtered_batch_shapes_against_oracle(handle, oracle_lib, shape):
+    # whole and half last chunks (cols % 8 == 0 / 4), batches that do not fill a warp's sixteen slots
+    rows, cols = shape
+    for batch in (1, 15, 333):
+        a = _batch_inputs(oracle_lib, batch, rows, cols, 21)
+        ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+        assert failed == 0
+        assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_filtered_batch_near_ties(handle, oracle_lib):
+    # leaders one to a few fp32 ulps apart, and exact ties: the fp32 pass cannot order them, the bound has to
+    # send those bids to the exact scan (and the lowest column has to win the exact ties)
+    rng = np.random.default_rng(5)
+    a = _batch_inputs(oracle_lib, 400, 24, 32, 8)
+    base = np.float32(0.75)
+    for b in range(400):
+        cols = rng.choice(32, size=6, replace=False)
+        ulps = rng.integers(0, 4, size=(24, 6))
+        a[b][:, cols] = (base + ulps * np.spacing(base)).astype(np.float32)
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_filtered_batch_coarse_grid_many_ties(handle, oracle_lib):
+    a = _batch_inputs(oracle_lib, 500, 32, 48, 13)
+    a = (np.ceil(a * 4) / 4).astype(np.float32)          # four distinct values: ties everywhere
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_filtered_batch_sparse_rows_and_single_edges(handle, oracle_lib):
+    # most coefficients are "no edge"; some rows keep a single edge (second best = -1e6, Auction.h:237):
+    # zero leaders switch the warp to the zero-aware pass, single edges always take the exact scan
+    rng = np.random.default_rng(6)
+    a = _batch_inputs(oracle_lib, 600, 12, 24, 17)
+    a[rng.random(a.shape) < 0.8] = 0.0
+    for r in range(12):
+        a[:, r, r] = np.maximum(a[:, r, r], 0.05)          # feasible: the diagonal is always an edge
+    a[::3, 0, 1:] = 0.0                                     # row 0 of every third problem: one edge only
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_filtered_batch_wide_magnitudes(handle, oracle_lib):
+    # coefficients outside [0, 1]: large values make large prices (the bound scales with the price), tiny values
+    # sit next to them, negative values are legal edges
+    rng = np.random.default_rng(7)
+    a = _batch_inputs(oracle_lib, 300, 16, 24, 19)
+    a[:100] *= np.float32(1000.0)
+    a[100:200] = (a[100:200] - np.float32(0.5)) * np.float32(4.0)
+    a[200:] *= (10.0 ** rng.integers(-6, 3, size=a[200:].shape)).astype(np.float32)
+    a[a == 0] = np.float32(0.5)
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    assert np.array_equal(handle.solve_batch(a), ref)
+
+
+def test_filtered_batch_large_batch_is_consistent(handle, oracle_lib):
+    # more problems than one resident wave holds slots for: every warp hands its slice out in turn; sampled
+    # against the oracle, and the whole batch against a second run split in two
+    import torch
+    n = 50000
+    t = torch.empty((n, 32, 48), dtype=torch.float32, device="cuda")
+    handle.generate_device(t.data_ptr(), n, 32, 48, 48, 1, seed=3, problem0=0)
+    out = torch.empty((n, 32), dtype=torch.int32, device="cuda")
+    handle.solve_batch_device(t.data_ptr(), n, 32, 48, out.data_ptr())
+    got = out.cpu().numpy()
+    assert (np.sort(got, axis=1)[:, 1:] != np.sort(got, axis=1)[:, :-1]).all() and got.min() >= 0 and got.max() < 48
+    idx = np.concatenate([np.arange(0, 64), np.arange(n - 64, n), np.arange(777, n, 997)])
+    a = np.stack([oracle_lib.generate(32, 48, 3, problem=int(b)) for b in idx])
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0 and np.array_equal(got[idx], ref)
+    out2 = torch.empty((n, 32), dtype=torch.int32, device="cuda")
+    h = 20011
+    handle.solve_batch_device(t.data_ptr(), h, 32, 48, out2.data_ptr())
+    handle.solve_batch_device(t[h:].data_ptr(), n - h, 32, 48, out2[h:].data_ptr())
+    assert torch.equal(out, out2)
+
+
 def test_batch_errors(handle):
     import auctionalgorithm_b200 as ab
     with pytest.raises(ab.B200LsapError) as e:

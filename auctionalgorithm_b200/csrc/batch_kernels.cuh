@@ -420,7 +420,8 @@ template <bool kZeroAware> __device__ __forceinline__ float filter_key(float a, 
 template <bool kZeroAware, int kM>
 __device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, const float* __restrict__ p32, int gl)
 {
-    Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE};
+    // two independent triples (halves of every chunk) keep two dependent chains in flight
+    Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE}, u3 = t3;
 #pragma unroll
     for (int m = 0; m < kM; m++)
     {
@@ -428,8 +429,9 @@ __device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, cons
         const float4 av = *reinterpret_cast<const float4*>(row + c);
         const float4 pp = *reinterpret_cast<const float4*>(p32 + c);
         top3_push2(t3, filter_key<kZeroAware>(av.x, pp.x, c), filter_key<kZeroAware>(av.y, pp.y, c + 1));
-        top3_push2(t3, filter_key<kZeroAware>(av.z, pp.z, c + 2), filter_key<kZeroAware>(av.w, pp.w, c + 3));
+        top3_push2(u3, filter_key<kZeroAware>(av.z, pp.z, c + 2), filter_key<kZeroAware>(av.w, pp.w, c + 3));
     }
+    top3_merge(t3, u3);
     return t3;
 }
 
@@ -478,7 +480,6 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     const int n = P.rows * P.cols;
     const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
     const unsigned lanes_before = (1u << lane) - 1u;
-    const unsigned pair = 3u << (2 * g);
     // this lane's last chunk lies beyond the row when cols % 8 == 4: never loaded, reads as "no edge"
     const bool last_chunk = kWhole || 8 * (kM - 1) + 4 * gl < P.cols;
     if (!last_chunk)

@@ -217,7 +217,7 @@ def run_sparse(handle, n: int = 20000, per_row: int = 40):
             "reference_cpu_s_offline": 441.0}
 
 
-def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int):
+def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int, with_host_legs: bool = False):
     """C3: this rank's shard of the batch, generated on the device (inputs resident in HBM)."""
     t = torch.empty((n_problems, 32, 48), dtype=torch.float32, device="cuda")
     out = torch.empty((n_problems, 32), dtype=torch.int32, device="cuda")
@@ -232,8 +232,35 @@ def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
+    extra = {}
+    if with_host_legs:
+        # end to end through the reference-facing batched entry (b200lsap_solve_batch_f32): HOST arrays in and out,
+        # the library's own copies inside the timed call
+        n_e2e = min(n_problems, 1 << 18)
+        host = t[:n_e2e].cpu().numpy()
+        handle.solve_batch(host[:1024])
+        t0 = time.perf_counter()
+        r2c = handle.solve_batch(host)
+        sec = time.perf_counter() - t0
+        assert (r2c >= 0).all()
+        extra["e2e"] = {"problems_per_s": n_e2e / sec, "problems": n_e2e, "h2d_bytes": int(host.nbytes),
+                        "d2h_bytes": int(r2c.nbytes), "input": "pageable host array [batch, 32, 48] fp32"}
+        # the reference has no batched entry: Auction<float, MatrixXf>::solve in a loop, here the CPU
+        # port of it (bit-identical, tests/test_oracle.py), one thread and all host threads, on a subsample
+        from oracle import pyoracle as po
+        cores = os.cpu_count() or 1
+        n_cpu = min(n_e2e, 1 << 16)
+        cpu = {"kind": "port", "cores": cores, "sample": f"first {n_cpu} problems of the same batch"}
+        for key, dbl, thr, cnt in (("float_1thread", False, 1, n_cpu // 8), ("float_all_threads", False, cores, n_cpu),
+                                   ("double_all_threads", True, cores, n_cpu)):
+            t0 = time.perf_counter()
+            ref, failed = po.oracle_batch(host[:cnt], use_double=dbl, n_threads=thr)
+            cpu[key + "_problems_per_s"] = cnt / (time.perf_counter() - t0)
+            if dbl:
+                cpu["gpu_result_identical_to_double_port"] = bool(failed == 0 and (ref == r2c[:cnt]).all())
+        extra["cpu_baseline"] = cpu
     del t, out
-    return ms, st["bid_bytes"]
+    return ms, st["bid_bytes"], extra
 
 
 def run_sharded(handle, torch, dist, rank: int, world: int, steps: int, rows: int, cols: int):
@@ -408,12 +435,14 @@ def main():
     torch.cuda.empty_cache()
 
     # ---- C3: batched 32x48 problems, sharded over ranks, no collective -------------------------
-    mht_ms, mht_bytes = run_mht(handle, torch, args.mht_problems, rank, max(args.steps, 3), 3)
+    mht_ms, mht_bytes, mht_extra = run_mht(handle, torch, args.mht_problems, rank, max(args.steps, 3), 3,
+                                           with_host_legs=(rank == 0 and world == 1 and not args.no_cpu))
     mht_ms = max_over_ranks(mht_ms)
     mht = {"problems_per_s": args.mht_problems * world / (mht_ms * 1e-3), "problems": args.mht_problems * world,
            "ms_per_step": mht_ms, "gbs_per_gpu": mht_bytes / mht_ms / 1e6,
            "frac_of_hbm_peak": mht_bytes / mht_ms / 1e6 / peak,
-           "layout": "row-major 32x48 fp32 problems, device-generated, resident in HBM; one shard per rank"}
+           "layout": "row-major 32x48 fp32 problems, device-generated, resident in HBM; one shard per rank",
+           "kernel": "k_auction_batch_filter<6,true,4,3>", **mht_extra}
     torch.cuda.empty_cache()
 
     # ---- C5: column-sharded big problem ------------------------------------------------------------

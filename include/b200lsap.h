@@ -172,7 +172,11 @@ int b200lsap_solve_csr_device_f64(b200lsap_handle* handle, const double* values_
 /*
  * Batched mode for MHT-style data association: `batch` independent rows x cols problems,
  * problem b at a + b*rows*cols, each stored in `layout` with ld = its minor dimension.
- * One warp solves one problem with its matrix held in shared memory.  rows <= cols <= 64.
+ * rows <= 32, rows <= cols <= 64.  The problems are solved in the reference's own Gauss-Seidel order
+ * (Auction.h:210-306 called once per problem, eps = eps_multiplier / cols), so every problem gets exactly
+ * the assignment Auction<double>::solve returns for its coefficients widened to double.  A warp works on
+ * sixteen problems at a time (two lanes each; cols % 4 == 0 and a 16-byte aligned matrix pointer) or on
+ * eight (four lanes each; any cols).  Coefficients must be finite.
  * row_to_col: int32[batch*rows].  Host and device-resident variants.
  */
 int b200lsap_solve_batch_f32(b200lsap_handle* handle, const float* a, int64_t batch, int32_t rows,

@@ -237,14 +237,20 @@ def run_mht(handle, torch, n_problems: int, rank: int, steps: int, warmup: int, 
         # end to end through the reference-facing batched entry (b200lsap_solve_batch_f32): HOST arrays in and out,
         # the library's own copies inside the timed call
         n_e2e = min(n_problems, 1 << 18)
-        host = t[:n_e2e].cpu().numpy()
+        host_t = torch.empty((n_e2e, 32, 48), dtype=torch.float32, pin_memory=True)
+        host_t.copy_(t[:n_e2e])
+        torch.cuda.synchronize()
+        host = host_t.numpy()
         handle.solve_batch(host[:1024])
+        handle.solve_batch(host)
         t0 = time.perf_counter()
         r2c = handle.solve_batch(host)
         sec = time.perf_counter() - t0
         assert (r2c >= 0).all()
         extra["e2e"] = {"problems_per_s": n_e2e / sec, "problems": n_e2e, "h2d_bytes": int(host.nbytes),
-                        "d2h_bytes": int(r2c.nbytes), "input": "pageable host array [batch, 32, 48] fp32"}
+                        "d2h_bytes": int(r2c.nbytes), "ms": sec * 1e3, "h2d_gbs": host.nbytes / sec / 1e9,
+                        "input": "pinned host array [batch, 32, 48] fp32, pageable result array; bound by the "
+                                 "6144 bytes per problem that cross PCIe, not by the kernel"}
         # the reference has no batched entry: Auction<float, MatrixXf>::solve in a loop, here the CPU
         # port of it (bit-identical, tests/test_oracle.py), one thread and all host threads, on a subsample
         from oracle import pyoracle as po

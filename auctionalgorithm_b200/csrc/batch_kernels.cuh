@@ -375,10 +375,14 @@ __global__ void __launch_bounds__(32, kWarpsPerSm) k_auction_batch_stream(BatchP
 //
 // Layout: 2 lanes per problem, 16 problems per warp; lane gl of a group owns the float4 chunks
 // 2m + gl of a row (columns 8m + 4gl .. +3), so a pair reads one 32-byte sector per instruction.
-// Prices (fp64 and their fp32 roundings), column owners, the assignment and two row buffers live in
-// shared memory (1136 bytes per 32x48 problem): a bid updates one entry of each with a store instead
-// of a select chain over registers, and the next row of the sweep arrives by cp.async while the current
-// one bids.  A warp owns a contiguous slice of the batch and hands the next problems to the groups that
+// The fp32 roundings of the prices, the column owners, two row buffers and the fp64 prices live in shared
+// memory, 880 bytes per 32x48 problem: a bid updates one entry of each with a store instead of a select
+// chain over registers.  The fp64 price is kept per ROW (the price of the column that row holds: a priced
+// column always has an owner, so 32 slots cover any number of columns), the assignment is read back from
+// the owners when a problem finishes, and the arrays are unpadded — 56 320 bytes per 4-warp CTA, four CTAs
+// = 16 warps per SM, which is what this latency-bound kernel needs most (12 warps with padded arrays and
+// per-column fp64 prices: 452 M problems/s; 16 warps: 470).  The next row of the sweep arrives by cp.async
+// while the current one bids.  A warp owns a contiguous slice of the batch and hands the next problems to the groups that
 // have finished (the bid count of a 32x48 problem ranges from 32 to 200+; a warp that waited for its
 // slowest group would idle 27 % of its lanes); it does so when two groups are waiting, so the divergent
 // hand-over code runs half as often.
@@ -435,19 +439,15 @@ __device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, cons
     return t3;
 }
 
-// stride (floats) of the per-problem fp32 arrays: >= 8 kM and = 8 mod 16, so the four problems of a
-// quarter warp read disjoint 8-bank windows with 128-bit loads
+// stride (floats) of the per-problem fp32 arrays
 __host__ __device__ inline int batch_filter_stride(int kM)
 {
-    int s = 8 * kM;
-    while ((s & 15) != 8)
-        s += 8;
-    return s;
+    return 8 * kM; // unpadded: a quarter warp's 128-bit accesses then take two wavefronts, 56 bytes per problem saved
 }
-// per warp: fp32 prices + two row buffers (3 x 16 x stride floats), fp64 prices, owners, assignment
+// per warp: fp32 prices + two row buffers (3 x 16 x stride floats), fp64 prices by row, owners
 __host__ __device__ inline size_t batch_filter_warp_bytes(int kM)
 {
-    return (size_t)16 * (3 * batch_filter_stride(kM) * 4 + 8 * kM * 8 + 8 * kM + 32);
+    return (size_t)16 * (3 * batch_filter_stride(kM) * 4 + kBatchMaxRows * 8 + 8 * kM);
 }
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc)
@@ -474,9 +474,15 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     unsigned char* wb = batch_smem + warp * batch_filter_warp_bytes(kM);
     float* p32 = reinterpret_cast<float*>(wb) + g * s32;                       // (float)price[col]
     float* rowbuf = reinterpret_cast<float*>(wb) + 16 * s32 + g * s32;         // + cur * 16 * s32: the bidding row
-    double* p64 = reinterpret_cast<double*>(wb + 3 * 16 * s32 * 4) + g * kC8;  // price[col] (Auction.h:58)
-    signed char* own = reinterpret_cast<signed char*>(wb + 3 * 16 * s32 * 4 + 16 * kC8 * 8) + g * kC8;
-    signed char* mc = reinterpret_cast<signed char*>(wb + 3 * 16 * s32 * 4 + 16 * kC8 * 9) + g * 32; // row -> column
+    // fp64 price (Auction.h:58) of the column a row holds, indexed by the ROW: at most `rows` columns are priced
+    // at any time (a priced column always has an owner), a column without an owner costs 0
+    double* p64r = reinterpret_cast<double*>(wb + 3 * 16 * s32 * 4) + g * kBatchMaxRows;
+    signed char* own = reinterpret_cast<signed char*>(wb + 3 * 16 * s32 * 4 + 16 * kBatchMaxRows * 8) + g * kC8;
+    auto price = [&](int c) -> double {
+        const int o = own[c];
+        const double q = p64r[o & 31]; // a group without a problem reads whatever its shared memory holds
+        return o >= 0 ? q : 0.0;
+    };
     const int n = P.rows * P.cols;
     const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
     const unsigned lanes_before = (1u << lane) - 1u;
@@ -515,14 +521,28 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             {
                 if (pb >= 0)
                 {
-                    // rows 16 gl .. 16 gl + 15 of the finished problem
-                    const int4 q = *reinterpret_cast<const int4*>(mc + 16 * gl);
-                    const int qq[4] = {q.x, q.y, q.z, q.w};
-                    int* out = P.row2col + pb * P.rows + 16 * gl;
+                    // row -> column from the owners (a failed problem: -1 everywhere)
+                    int* out = P.row2col + pb * P.rows;
+                    if (fail)
+                    {
+                        for (int r = gl; r < P.rows; r += 2)
+                            out[r] = -1;
+                    }
+                    else
+                    {
 #pragma unroll
-                    for (int k = 0; k < 16; k++)
-                        if (16 * gl + k < P.rows)
-                            out[k] = (int)(signed char)(qq[k >> 2] >> (8 * (k & 3)));
+                        for (int m = 0; m < kM; m++)
+                        {
+                            const int q = *reinterpret_cast<const int*>(own + 8 * m + 4 * gl);
+#pragma unroll
+                            for (int e = 0; e < 4; e++)
+                            {
+                                const int o = (int)(signed char)(q >> (8 * e));
+                                if (o >= 0)
+                                    out[o] = 8 * m + 4 * gl + e;
+                            }
+                        }
+                    }
                     if (fail && gl == 0)
                         *P.status = fail;
                 }
@@ -539,13 +559,10 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                         // a column beyond the row is priced out of the single-precision pass
                         const float p0 = (m < kM - 1 || last_chunk) ? 0.f : 3.0e38f;
                         *reinterpret_cast<float4*>(p32 + c) = make_float4(p0, p0, p0, p0);
-                        *reinterpret_cast<double2*>(p64 + c) = make_double2(0.0, 0.0);
-                        *reinterpret_cast<double2*>(p64 + c + 2) = make_double2(0.0, 0.0);
                         *reinterpret_cast<int*>(own + c) = -1;
                         if (m < kM - 1 || last_chunk)
                             cp_async16(nb + c, A + c);
                     }
-                    *reinterpret_cast<int4*>(mc + 16 * gl) = make_int4(-1, -1, -1, -1);
                     pf_i = 0;
                     unassigned = all_rows;
                     todo = 0;
@@ -623,7 +640,9 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         // the two leaders, exactly (Auction.h:131-150: strict '>' keeps the lowest column among equals)
         const int c1 = __float_as_uint(t3.m1) & 63, c2 = __float_as_uint(t3.m2) & 63;
         const float a1 = row[c1], a2 = row[c2];
-        const double d1 = (double)a1 - p64[c1], d2 = (double)a2 - p64[c2]; // two conversions per bid: no XU pressure
+        const int o1 = own[c1], o2 = own[c2];
+        const double q1 = p64r[o1 & 31], q2 = p64r[o2 & 31];
+        const double d1 = (double)a1 - (o1 >= 0 ? q1 : 0.0), d2 = (double)a2 - (o2 >= 0 ? q2 : 0.0);
         const bool first = d1 > d2 || (d1 == d2 && c1 < c2);
         int j = first ? c1 : c2;
         float aj = first ? a1 : a2;
@@ -646,10 +665,10 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                 if (m < kM - 1 || last_chunk)
                 {
                     const float4 av = *reinterpret_cast<const float4*>(row + c);
-                    top2_push(t, av.x, p64[c], c);
-                    top2_push(t, av.y, p64[c + 1], c + 1);
-                    top2_push(t, av.z, p64[c + 2], c + 2);
-                    top2_push(t, av.w, p64[c + 3], c + 3);
+                    top2_push(t, av.x, price(c), c);
+                    top2_push(t, av.y, price(c + 1), c + 1);
+                    top2_push(t, av.z, price(c + 2), c + 2);
+                    top2_push(t, av.w, price(c + 3), c + 3);
                 }
             }
             const Top2<float> o = top2_shfl_xor(t, 1);
@@ -672,8 +691,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             if (gl == 0)
             {
                 own[j] = (signed char)i;
-                mc[i] = (signed char)j;
-                p64[j] = bid;
+                p64r[i] = bid;
                 p32[j] = b32;
             }
             pmax = fmaxf(pmax, b32);

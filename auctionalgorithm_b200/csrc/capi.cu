@@ -1001,7 +1001,7 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     if (!smem_mode && filter_mode && cols % 4 == 0 && ((uintptr_t)a_dev_row_major & 15) == 0)
     {
         // 16 problems per warp, four warps per CTA, one resident wave; a warp takes a slice of the batch
-        constexpr int kFW = 4, kFC = 3;
+        constexpr int kFW = 4, kFC = 4;
 #define B200LSAP_FILTER(M) k_auction_batch_filter<M, true, kFW, kFC>, k_auction_batch_filter<M, false, kFW, kFC>
         static const BatchKernel kf[16] = {B200LSAP_FILTER(1), B200LSAP_FILTER(2), B200LSAP_FILTER(3),
                                            B200LSAP_FILTER(4), B200LSAP_FILTER(5), B200LSAP_FILTER(6),

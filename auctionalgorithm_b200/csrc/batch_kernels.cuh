@@ -421,15 +421,35 @@ template <bool kZeroAware> __device__ __forceinline__ float filter_key(float a, 
     return __uint_as_float((__float_as_uint(d) & ~63u) | (unsigned)col);
 }
 
+// The arrays are unpadded, so the problems of a quarter warp start 8 kM floats apart: for kM = 2 mod 4 two of
+// the four share a 32-byte bank window, for kM = 0 mod 4 all four do.  The groups therefore walk their chunks in
+// rotated order (group g starts at chunk rot(g)): at every step the four 128-bit accesses of a quarter warp
+// then fall into different windows.  The order is free in the single-precision pass (keys are distinct) and
+// in the copies; the exact scan keeps increasing columns.
+template <int kM> __device__ __forceinline__ int filter_rot(int g)
+{
+    return kM % 4 == 0 ? (g & 3) : (kM % 4 == 2 ? ((g >> 1) & 1) : 0);
+}
+// first column of the chunk a lane visits at step m
+template <int kM> __device__ __forceinline__ int filter_chunk(int m, int rot, int gl)
+{
+    constexpr int kRotMax = kM % 4 == 0 ? 3 : (kM % 4 == 2 ? 1 : 0);
+    int mm = m + rot;
+    if (m + kRotMax >= kM && mm >= kM) // only the last kRotMax steps can wrap
+        mm -= kM;
+    return 8 * mm + 4 * gl;
+}
+
 template <bool kZeroAware, int kM>
-__device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, const float* __restrict__ p32, int gl)
+__device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, const float* __restrict__ p32, int gl,
+                                             int rot)
 {
     // two independent triples (halves of every chunk) keep two dependent chains in flight
     Top3f t3 = {B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE, B200LSAP_FILTER_NONE}, u3 = t3;
 #pragma unroll
     for (int m = 0; m < kM; m++)
     {
-        const int c = 8 * m + 4 * gl;
+        const int c = filter_chunk<kM>(m, rot, gl);
         const float4 av = *reinterpret_cast<const float4*>(row + c);
         const float4 pp = *reinterpret_cast<const float4*>(p32 + c);
         top3_push2(t3, filter_key<kZeroAware>(av.x, pp.x, c), filter_key<kZeroAware>(av.y, pp.y, c + 1));
@@ -486,6 +506,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
     const int n = P.rows * P.cols;
     const unsigned all_rows = P.rows == 32 ? kFullMask : ((1u << P.rows) - 1u);
     const unsigned lanes_before = (1u << lane) - 1u;
+    const int rot = filter_rot<kM>(g);
     // this lane's last chunk lies beyond the row when cols % 8 == 4: never loaded, reads as "no edge"
     const bool last_chunk = kWhole || 8 * (kM - 1) + 4 * gl < P.cols;
     if (!last_chunk)
@@ -600,8 +621,11 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                 float* cb = rowbuf + cur * 16 * s32;
 #pragma unroll
                 for (int m = 0; m < kM; m++)
-                    if (m < kM - 1 || last_chunk)
-                        cp_async16(cb + 8 * m + 4 * gl, row + 8 * m + 4 * gl);
+                {
+                    const int c = filter_chunk<kM>(m, rot, gl);
+                    if (c < 8 * (kM - 1) || last_chunk)
+                        cp_async16(cb + c, row + c);
+                }
             }
         }
         cp_async_commit();
@@ -617,8 +641,11 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             float* nb = rowbuf + (cur ^ 1) * 16 * s32;
 #pragma unroll
             for (int m = 0; m < kM; m++)
-                if (m < kM - 1 || last_chunk)
-                    cp_async16(nb + 8 * m + 4 * gl, row2 + 8 * m + 4 * gl);
+            {
+                const int c = filter_chunk<kM>(m, rot, gl);
+                if (c < 8 * (kM - 1) || last_chunk)
+                    cp_async16(nb + c, row2 + c);
+            }
         }
         else
             pf_i = -1;
@@ -627,7 +654,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         const float* row = rowbuf + cur * 16 * s32;
 
         // single-precision pass over this lane's chunks (its own copies: no synchronisation needed yet)
-        Top3f t3 = zero_aware ? filter_pass<true, kM>(row, p32, gl) : filter_pass<false, kM>(row, p32, gl);
+        Top3f t3 = zero_aware ? filter_pass<true, kM>(row, p32, gl, rot) : filter_pass<false, kM>(row, p32, gl, rot);
         {
             Top3f o;
             o.m1 = __shfl_xor_sync(kFullMask, t3.m1, 1);

@@ -440,6 +440,16 @@ template <int kM> __device__ __forceinline__ int filter_chunk(int m, int rot, in
     return 8 * mm + 4 * gl;
 }
 
+// the same relative to the lane's first chunk (column 8 rot + 4 gl): a constant for the steps that cannot wrap, so
+// pointers formed once per row as base + first chunk take immediate offsets
+template <int kM> __device__ __forceinline__ int filter_chunk_rel(int m, int rot)
+{
+    constexpr int kRotMax = kM % 4 == 0 ? 3 : (kM % 4 == 2 ? 1 : 0);
+    if (m + kRotMax >= kM && m + rot >= kM)
+        return 8 * (m - kM);
+    return 8 * m;
+}
+
 template <bool kZeroAware, int kM>
 __device__ __forceinline__ Top3f filter_pass(const float* __restrict__ row, const float* __restrict__ p32, int gl,
                                              int rot)
@@ -637,14 +647,14 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         if (ahead != 0)
         {
             pf_i = __ffs(ahead) - 1;
-            const float* row2 = A + pf_i * P.cols;
-            float* nb = rowbuf + (cur ^ 1) * 16 * s32;
+            const float* row2 = A + pf_i * P.cols + (8 * rot + 4 * gl); // this lane's first chunk
+            float* nb = rowbuf + (cur ^ 1) * 16 * s32 + (8 * rot + 4 * gl);
 #pragma unroll
             for (int m = 0; m < kM; m++)
             {
-                const int c = filter_chunk<kM>(m, rot, gl);
-                if (c < 8 * (kM - 1) || last_chunk)
-                    cp_async16(nb + c, row2 + c);
+                const int rel = filter_chunk_rel<kM>(m, rot);
+                if (kWhole || filter_chunk<kM>(m, rot, gl) < 8 * (kM - 1) || last_chunk)
+                    cp_async16(nb + rel, row2 + rel);
             }
         }
         else

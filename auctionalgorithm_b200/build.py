@@ -15,8 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libb200lsap.so")
 SOURCES = ["capi.cu"]
-HEADERS = ["common.cuh", "dense_state.cuh", "dense_kernels.cuh", "batch_kernels.cuh", "shard_kernels.cuh",
-           "dense_cache.cuh", "narrow_kernel.cuh"]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith(".cuh"))  # every header capi.cu may include
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--shared",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O3"]
 

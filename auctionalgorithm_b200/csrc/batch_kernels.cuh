@@ -26,6 +26,16 @@ constexpr int kBatchColsPerLane = 8;                 // kBatchMaxCols / kBatchGr
 constexpr int kBatchMaxRows = 32;
 constexpr int kBatchMaxCols = 64;
 
+// Device-side control block of a batched launch (zeroed by the host before every launch).
+struct BatchCtrl
+{
+    unsigned long long next; // dynamic hand-out: the first problem no warp has reserved yet
+    int status;              // b200lsap_status of a failed problem, 0 when none failed
+    int takeovers;           // problems that reached the bid cap and were finished by a whole warp
+    int max_bids;            // largest bid count of a problem in this launch
+    int pad;
+};
+
 struct BatchParams
 {
     const float* a;   // [batch][rows*cols], row-major inside a problem
@@ -34,7 +44,10 @@ struct BatchParams
     int rows, cols;
     double eps;       // eps_multiplier / cols (Auction.h:55)
     int max_bids;     // watchdog per problem
-    int* status;      // device flag, set to a b200lsap_status on failure
+    int* status;      // device flag, set to a b200lsap_status on failure (= &ctl->status)
+    BatchCtrl* ctl;   // filtered kernel: hand-out counter and statistics
+    int cap;          // filtered kernel: a problem with this many bids is finished by its whole warp
+    int chunk;        // filtered kernel: problems per reservation of the hand-out counter
 };
 
 // One warp per CTA (no block-level synchronisation anywhere); shared memory = 4 problems.
@@ -492,6 +505,224 @@ template <int kPending> __device__ __forceinline__ void cp_async_wait()
     asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------
+// Whole-warp takeover.  The bid count of a 32x48 problem has a long tail (mean 44; about 500 problems
+// in a million need more than 96 bids, one or two need more than a thousand: price wars in which a few
+// rows raise a few prices by eps per bid).  Two lanes play such a problem at ~0.7 us per bid while the
+// rest of the launch has long finished, so a group that reaches P.cap bids hands its problem to its
+// whole warp, which CONTINUES the group's Gauss-Seidel sweep (Auction.h:210-306) from its state
+// (prices, owners, unassigned rows, position in the sweep): same bids in the same order, same result.
+//
+//  * The matrix goes into the warp's row buffers (exactly 32 x 8 kM floats); fp64 prices and owners live
+//    per COLUMN in the group's own arrays.
+//  * A full scan is the filter of the two-lane pass across the warp: lane l evaluates columns l and l + 32,
+//    keys a - (float)p with the column in the six low bits, the largest keys one by one with redux.sync on
+//    the order-preserving integer image of the keys, the two leaders evaluated exactly, the third key as
+//    the certificate, and the exact fp64 top-2 of every column (shuffle merge) when the certificate fails.
+//  * Row caches (the narrow rounds' idea, dense_cache.cuh, in miniature): a full scan of row r leaves the
+//    columns of its four largest keys, their coefficients and an upper bound of a - p over every OTHER
+//    column (the fifth key plus the filter's error margin) in the registers of lane r.  Prices never
+//    decrease, so the bound holds for the rest of the solve.  The next bid of row r evaluates those four
+//    columns exactly at the current prices — lane r alone, ~40 dependent instructions instead of ~100 —
+//    and is the reference's bid whenever its second-best value lies strictly above the bound (nothing
+//    outside the cache can then be best or second best); otherwise the row is scanned again.  A price war
+//    is rows re-bidding for the same few columns: almost all of its bids hit.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned ord_u32(float x)
+{
+    const unsigned b = __float_as_uint(x);
+    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u); // larger float <=> larger unsigned
+}
+__device__ __forceinline__ float ord_f32(unsigned k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+}
+
+// what the single-precision keys may have lost against the exact a - p (two-lane pass: same bound)
+__device__ __forceinline__ float filter_bound(float k, float pmax)
+{
+    return k + (fabsf(k) * 3.0517578125e-5f + pmax * 4.76837158203125e-7f + 1e-30f);
+}
+
+// Byte offsets into the kernel's dynamic shared memory: rows_off = the warp's row buffers (>= rows * cols floats,
+// + 64 floats of the warp's own arrays behind them), own_off / p64_off / p32_off = the group's owner, fp64 price
+// (by row) and fp32 price arrays; unassigned / todo / bids / pmax: the group's sweep state.  Writes the problem's
+// row -> column (or -1 everywhere and *status on failure); returns the final bid count.
+__device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_off, unsigned p64_off, unsigned p32_off,
+                                              const float* __restrict__ A, int* __restrict__ out, int rows, int cols,
+                                              double eps, int max_bids, int* status, unsigned unassigned, unsigned todo,
+                                              int bids, float pmax)
+{
+    extern __shared__ __align__(16) unsigned char batch_smem[];
+    float* sA = reinterpret_cast<float*>(batch_smem + rows_off);
+    signed char* ownc = reinterpret_cast<signed char*>(batch_smem + own_off);   // owner of a column (stays as it is)
+    double* pc_lo = reinterpret_cast<double*>(batch_smem + p64_off);            // price of columns 0..31
+    double* pc_hi = reinterpret_cast<double*>(batch_smem + p32_off) - 32;       // price of columns 32..
+    auto pc = [&](int c) -> double* { return (c < 32 ? pc_lo : pc_hi) + c; };
+    const int lane = threadIdx.x & 31;
+    const int n4 = rows * cols / 4;
+    for (int k = lane; k < n4; k += 32)
+        reinterpret_cast<float4*>(sA)[k] = __ldg(reinterpret_cast<const float4*>(A) + k);
+    const int cA = lane, cB = lane + 32;
+    const bool hasA = cA < cols, hasB = cB < cols;
+    {
+        // prices by row (the two-lane pass) -> prices by column (Auction.h:58), in place
+        const int oA = hasA ? (int)ownc[cA] : -1, oB = hasB ? (int)ownc[cB] : -1;
+        const double pA = oA >= 0 ? pc_lo[oA] : 0.0, pB = oB >= 0 ? pc_lo[oB] : 0.0;
+        __syncwarp();
+        if (hasA)
+            pc_lo[cA] = pA;
+        if (hasB)
+            pc_hi[cB] = pB;
+    }
+    // this lane's row: cached columns (ascending, one per byte), their coefficients, bound of everything else
+    unsigned cc = 0;
+    double ca0 = 0.0, ca1 = 0.0, ca2 = 0.0, ca3 = 0.0;
+    double cbound = CUDART_INF; // no cache yet: every bid misses
+    int fail = 0;
+    while (unassigned != 0)
+    {
+        if (todo == 0)
+            todo = unassigned; // next forward sweep (Auction.h:66-68, :220)
+        const int i = __ffs(todo) - 1;
+        todo &= todo - 1;
+        __syncwarp(); // the previous bid's price and owner are visible
+        // every lane evaluates its own row's cache (one instruction stream); lane i's answer is the bid
+        int j, prev;
+        double bid;
+        {
+            const int c0 = cc & 63, c1 = (cc >> 8) & 63, c2 = (cc >> 16) & 63, c3 = cc >> 24;
+            const double d0 = ca0 - *pc(c0), d1 = ca1 - *pc(c1), d2 = ca2 - *pc(c2), d3 = ca3 - *pc(c3);
+            const int o0 = ownc[c0], o1 = ownc[c1], o2 = ownc[c2], o3 = ownc[c3];
+            // strict '>' in ascending column order keeps the lowest column among equals (Auction.h:136)
+            const bool g01 = d1 > d0, g23 = d3 > d2;
+            const double vA = g01 ? d1 : d0, wA = g01 ? d0 : d1, vB = g23 ? d3 : d2, wB = g23 ? d2 : d3;
+            const bool gB = vB > vA;
+            const double w = gB ? fmax(vA, wB) : fmax(vB, wA); // second best, may equal the best (Auction.h:147-148)
+            const double aj = gB ? (g23 ? ca3 : ca2) : (g01 ? ca1 : ca0);
+            const int mj = gB ? (g23 ? c3 : c2) : (g01 ? c1 : c0);
+            const int mo = gB ? (g23 ? o3 : o2) : (g01 ? o1 : o0);
+            const bool hit = w > cbound;
+            j = __shfl_sync(kFullMask, hit ? mj : -1, i);
+            prev = __shfl_sync(kFullMask, mo, i);
+            bid = __shfl_sync(kFullMask, aj - w + eps, i); // Auction.h:250
+        }
+        if (j < 0)
+        {
+            // full scan of row i, every lane two columns
+            const float* row = sA + i * cols;
+            const float a0 = hasA ? row[cA] : 0.f, a1 = hasB ? row[cB] : 0.f; // 0: no edge (Auction.h:134)
+            const double pA = hasA ? pc_lo[cA] : 0.0, pB = hasB ? pc_hi[cB] : 0.0;
+            const unsigned uA = ord_u32(filter_key<true>(a0, __double2float_rn(pA), cA)),
+                           uB = ord_u32(filter_key<true>(a1, __double2float_rn(pB), cB));
+            // keys are distinct (the column is part of the key): each redux removes exactly one of them
+            unsigned x = max(uA, uB), y = min(uA, uB);
+            unsigned u[5];
+#pragma unroll
+            for (int t = 0; t < 5; t++)
+            {
+                u[t] = __reduce_max_sync(kFullMask, x);
+                if (x == u[t])
+                {
+                    x = y;
+                    y = 0u;
+                }
+            }
+            const float k1 = ord_f32(u[0]), k2 = ord_f32(u[1]), k3 = ord_f32(u[2]), k4 = ord_f32(u[3]), k5 = ord_f32(u[4]);
+            // the two leaders, exactly (Auction.h:131-150: strict '>' keeps the lowest column among equals)
+            int c1 = __float_as_uint(k1) & 63, c2 = __float_as_uint(k2) & 63;
+            const float e1 = row[c1], e2 = row[c2];
+            const double d1 = (double)e1 - *pc(c1), d2 = (double)e2 - *pc(c2);
+            const bool first = d1 > d2 || (d1 == d2 && c1 < c2);
+            j = first ? c1 : c2;
+            float aj = first ? e1 : e2;
+            double wv = first ? d2 : d1;
+            // nothing else can reach the second-best value
+            const bool fast = k2 > -5.0e5f && wv > (double)filter_bound(k3, pmax) && e1 != 0.f && e2 != 0.f;
+            if (!fast)
+            {
+                Top2<float> t = top2_empty<float>();
+                top2_push(t, a0, pA, cA);
+                top2_push(t, a1, pB, cB);
+                top2_warp_reduce(t);
+                j = t.j;
+                aj = t.a;
+                wv = t.w;
+            }
+            if (j < 0)
+            {
+                fail = 2; // a row without an edge: the reference would never return
+                break;
+            }
+            bid = (double)aj - wv + eps; // Auction.h:250
+            prev = ownc[j];
+            // row i's cache: the columns of the four largest keys in ascending order; every other column's exact
+            // a - p lies below the fifth key plus the filter's margin, now and for ever
+            int c3 = __float_as_uint(k3) & 63, c4 = __float_as_uint(k4) & 63;
+            int lo, hi;
+#define B200LSAP_CSWAP(a, b) lo = min(a, b), hi = max(a, b), a = lo, b = hi
+            B200LSAP_CSWAP(c1, c2);
+            B200LSAP_CSWAP(c3, c4);
+            B200LSAP_CSWAP(c1, c3);
+            B200LSAP_CSWAP(c2, c4);
+            B200LSAP_CSWAP(c2, c3);
+#undef B200LSAP_CSWAP
+            // (a key of a column beyond the row belongs to no edge: cached as column 0 with no coefficient)
+            const bool in1 = c1 < cols, in2 = c2 < cols, in3 = c3 < cols, in4 = c4 < cols;
+            c1 = in1 ? c1 : 0, c2 = in2 ? c2 : 0, c3 = in3 ? c3 : 0, c4 = in4 ? c4 : 0;
+            const float f1 = in1 ? row[c1] : 0.f, f2 = in2 ? row[c2] : 0.f, f3 = in3 ? row[c3] : 0.f,
+                        f4 = in4 ? row[c4] : 0.f;
+            if (lane == i)
+            {
+                cc = (unsigned)c1 | ((unsigned)c2 << 8) | ((unsigned)c3 << 16) | ((unsigned)c4 << 24);
+                // a column without an edge can neither win nor be second: its value sinks below every bound
+                ca0 = f1 != 0.f ? (double)f1 : -1e300;
+                ca1 = f2 != 0.f ? (double)f2 : -1e300;
+                ca2 = f3 != 0.f ? (double)f3 : -1e300;
+                ca3 = f4 != 0.f ? (double)f4 : -1e300;
+                cbound = (double)filter_bound(k5, pmax);
+            }
+        }
+        const float b32 = __double2float_rn(bid);
+        if (lane == i)
+        {
+            *pc(j) = bid;
+            ownc[j] = (signed char)i;
+        }
+        pmax = fmaxf(pmax, b32);
+        unassigned &= ~(1u << i);
+        if (prev >= 0)
+        {
+            unassigned |= 1u << prev; // Auction.h:270
+            if (prev > i)
+                todo |= 1u << prev; // unlocked ahead of the sweep position: visited in this sweep
+        }
+        if (++bids > max_bids)
+        {
+            fail = 3;
+            break;
+        }
+    }
+    __syncwarp();
+    if (fail)
+    {
+        for (int r = lane; r < rows; r += 32)
+            out[r] = -1;
+        if (lane == 0)
+            *status = fail;
+    }
+    else
+    {
+        const int oA = hasA ? (int)ownc[cA] : -1, oB = hasB ? (int)ownc[cB] : -1;
+        if (oA >= 0)
+            out[oA] = cA;
+        if (oB >= 0)
+            out[oB] = cB;
+    }
+    __syncwarp();
+    return bids;
+}
+
 // kWhole: cols % 8 == 0, every lane's last chunk lies inside the row (no predicate around its copies)
 template <int kM, bool kWhole, int kWarps, int kCtasPerSm>
 __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filter(BatchParams P)
@@ -526,10 +757,22 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         *reinterpret_cast<float4*>(rowbuf + 16 * s32 + 8 * (kM - 1) + 4 * gl) = z;
     }
 
-    // this warp's slice of the batch
-    const long long W = (long long)gridDim.x * kWarps, w = (long long)warp * gridDim.x + blockIdx.x;
-    long long next = P.batch / W * w + min(w, P.batch % W);
-    const long long end = next + P.batch / W + (w < P.batch % W ? 1 : 0);
+    // Dynamic hand-out: a warp reserves P.chunk problems at a time from one counter, so nobody owns a slice whose
+    // slow problems it must play alone; the reservation after the current one is requested a reservation ahead
+    // (lane 0 holds it: the atomic's latency is spent while the current problems bid).
+    long long next, end, nbase = 0;
+    {
+        unsigned long long b0 = 0;
+        if (lane == 0)
+        {
+            b0 = atomicAdd(&P.ctl->next, (unsigned long long)P.chunk);
+            nbase = b0 < (unsigned long long)P.batch ? (long long)atomicAdd(&P.ctl->next, (unsigned long long)P.chunk)
+                                                     : (long long)b0;
+        }
+        next = (long long)__shfl_sync(kFullMask, b0, 0);
+        end = min(next + P.chunk, P.batch);
+    }
+    int max_seen = 0;               // largest bid count among this lane's problems
 
     long long pb = -1;              // the group's problem
     const float* __restrict__ A = P.a;
@@ -548,6 +791,16 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         const unsigned am = __ballot_sync(kFullMask, unassigned != 0);
         if (__popc(nm) >= 4 || (nm != 0 && am == 0))
         {
+            const int k = __popc(nm) >> 1;                 // groups that want a problem
+            const int r = __popc(nm & lanes_before) >> 1;  // this group's rank among them
+            const long long avail = max(end - next, 0ll);
+            const bool sw = avail < k;                     // the current reservation does not cover them: open the next
+            long long nb = 0, nend = 0;
+            if (sw)
+            {
+                nb = __shfl_sync(kFullMask, nbase, 0);
+                nend = min(nb + P.chunk, P.batch);
+            }
             if (need)
             {
                 if (pb >= 0)
@@ -556,8 +809,8 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                     int* out = P.row2col + pb * P.rows;
                     if (fail)
                     {
-                        for (int r = gl; r < P.rows; r += 2)
-                            out[r] = -1;
+                        for (int rr = gl; rr < P.rows; rr += 2)
+                            out[rr] = -1;
                     }
                     else
                     {
@@ -577,12 +830,18 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                     if (fail && gl == 0)
                         *P.status = fail;
                 }
-                const long long np = next + (__popc(nm & lanes_before) >> 1);
-                if (np < end)
+                max_seen = max(max_seen, bids);
+                bids = 0;
+                long long np = -1;
+                if (r < avail)
+                    np = next + r;
+                else if (sw && nb + (r - avail) < nend)
+                    np = nb + (r - avail);
+                if (np >= 0)
                 {
                     pb = np;
                     A = P.a + pb * n;
-                    float* nb = rowbuf + (cur ^ 1) * 16 * s32;
+                    float* nbuf = rowbuf + (cur ^ 1) * 16 * s32;
 #pragma unroll
                     for (int m = 0; m < kM; m++)
                     {
@@ -592,7 +851,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                         *reinterpret_cast<float4*>(p32 + c) = make_float4(p0, p0, p0, p0);
                         *reinterpret_cast<int*>(own + c) = -1;
                         if (m < kM - 1 || last_chunk)
-                            cp_async16(nb + c, A + c);
+                            cp_async16(nbuf + c, A + c);
                     }
                     pf_i = 0;
                     unassigned = all_rows;
@@ -603,14 +862,60 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                 }
                 else
                 {
-                    pb = -1;
-                    done = true;
+                    pb = -1;            // nothing in reach this time; nothing left at all once the counter has passed the batch
+                    done = sw && nb >= P.batch;
                 }
             }
-            next += __popc(nm) >> 1;
+            if (sw)
+            {
+                next = nb + max(0ll, min((long long)k - avail, nend - nb));
+                end = nend;
+                if (lane == 0)
+                    nbase = nb < P.batch ? (long long)atomicAdd(&P.ctl->next, (unsigned long long)P.chunk) : nb;
+            }
+            else
+                next += k;
             __syncwarp();
             if (__all_sync(kFullMask, done))
                 break;
+        }
+
+        // a problem that has reached the bid cap is finished by the whole warp (batch_warp_finish)
+        const unsigned cm = __ballot_sync(kFullMask, unassigned != 0 && bids >= P.cap);
+        if (cm != 0)
+        {
+            const int src = __ffs(cm) - 1;
+            const long long t_pb = __shfl_sync(kFullMask, pb, src);
+            const unsigned t_un = __shfl_sync(kFullMask, unassigned, src), t_todo = __shfl_sync(kFullMask, todo, src);
+            const int t_bids = __shfl_sync(kFullMask, bids, src);
+            const float t_pmax = __shfl_sync(kFullMask, pmax, src);
+            cp_async_wait<0>(); // the row buffers are about to hold the whole matrix
+            __syncwarp();
+            const int tg = src >> 1;
+            const unsigned wb_off = warp * (unsigned)batch_filter_warp_bytes(kM);
+            const int total = batch_warp_finish(
+                wb_off + 16 * s32 * 4, wb_off + 3 * 16 * s32 * 4 + 16 * kBatchMaxRows * 8 + tg * kC8,
+                wb_off + 3 * 16 * s32 * 4 + tg * kBatchMaxRows * 8, wb_off + tg * s32 * 4, P.a + t_pb * n,
+                P.row2col + t_pb * P.rows, P.rows, P.cols, P.eps, P.max_bids, P.status, t_un, t_todo, t_bids, t_pmax);
+            if (lane == 0)
+                atomicAdd(&P.ctl->takeovers, 1);
+            max_seen = max(max_seen, total);
+            if (g == tg)
+            {
+                pb = -1; // already written
+                unassigned = 0;
+                todo = 0;
+                bids = 0;
+            }
+            pf_i = -1; // every group's prefetched row is gone
+            if (!last_chunk)
+            {
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4*>(rowbuf + 8 * (kM - 1) + 4 * gl) = z;
+                *reinterpret_cast<float4*>(rowbuf + 16 * s32 + 8 * (kM - 1) + 4 * gl) = z;
+            }
+            __syncwarp();
+            continue;
         }
 
         if (todo == 0)
@@ -755,6 +1060,10 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
         __syncwarp();
     }
     cp_async_wait<0>();
+    max_seen = max(max_seen, bids);
+    max_seen = __reduce_max_sync(kFullMask, max_seen);
+    if (lane == 0 && max_seen > 0)
+        atomicMax(&P.ctl->max_bids, max_seen);
 }
 
 

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -58,8 +59,10 @@ struct b200lsap_handle
     bool own_stream = false;
     std::string err;
     DevBuf a, staging, csr_ptr, csr_col, csr_val, prices, pricesf, cand, cache, cache_hdr, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
-        ctrl, out64, batch_in, batch_out;
+        ctrl, out64, batch_in, batch_out, batch_ctrl;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
+    BatchCtrl* h_bctrl = nullptr; // pinned mirror of the batched launch's control block
+    std::map<const void*, int> occupancy; // kernel -> resident CTAs per SM (attributes set once per handle)
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t last_cols = 0; // prices of the last dense solve are valid for this many columns
     const void* last_a = nullptr; // matrix of that solve when it was used in place (candidate lists stay valid)
@@ -171,7 +174,8 @@ int b200lsap_create(b200lsap_handle** out, int device)
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMallocHost((void**)&h->h_ctrl, sizeof(DenseCtrl)) != cudaSuccess)
+        cudaMallocHost((void**)&h->h_ctrl, sizeof(DenseCtrl)) != cudaSuccess ||
+        cudaMallocHost((void**)&h->h_bctrl, sizeof(BatchCtrl)) != cudaSuccess)
     {
         delete h;
         return B200LSAP_ERR_CUDA;
@@ -211,13 +215,15 @@ int b200lsap_destroy(b200lsap_handle* h)
     cudaStreamSynchronize(h->stream);
     for (DevBuf* b : {&h->a, &h->staging, &h->csr_ptr, &h->csr_col, &h->csr_val, &h->prices, &h->pricesf, &h->cand, &h->cache, &h->cache_hdr, &h->narrow, &h->profits, &h->slots, &h->owner, &h->row2col, &h->bid_col,
                       &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
-                      &h->batch_out})
+                      &h->batch_out, &h->batch_ctrl})
         b->release();
     for (auto& e : h->ev)
         if (e)
             cudaEventDestroy(e);
     if (h->h_ctrl)
         cudaFreeHost(h->h_ctrl);
+    if (h->h_bctrl)
+        cudaFreeHost(h->h_bctrl);
     if (h->own_stream && h->stream)
         cudaStreamDestroy(h->stream);
     delete h;
@@ -955,8 +961,25 @@ int b200lsap_solve_csr_device_f64(b200lsap_handle* h, const double* values, cons
 namespace
 {
 
+// Resident CTAs per SM of a batched kernel; its shared-memory attribute is set the first time a handle sees it
+// (not on every call: a 100-problem MHT frame would pay two driver queries per solve).
+int batch_occupancy(b200lsap_handle* h, const void* kernel, int threads, size_t smem, int& per_sm)
+{
+    auto it = h->occupancy.find(kernel);
+    if (it != h->occupancy.end())
+    {
+        per_sm = it->second;
+        return B200LSAP_OK;
+    }
+    if (smem > 0)
+        CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+    h->occupancy[kernel] = per_sm;
+    return B200LSAP_OK;
+}
+
 int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, int rows, int cols,
-              const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats)
+              const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats, bool sync = true)
 {
     b200lsap_options o;
     b200lsap_options_default(&o);
@@ -972,25 +995,16 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     P.cols = cols;
     P.eps = o.eps_multiplier / (double)cols;
     P.max_bids = o.max_rounds > 0 ? (int)(o.max_rounds > 0x7fffffff ? 0x7fffffff : o.max_rounds) : 1000000;
-    CU(h->ctrl.ensure(sizeof(DenseCtrl)));
-    P.status = &h->ctrl.as<DenseCtrl>()->status;
-    CU(cudaMemsetAsync(P.status, 0, sizeof(int), h->stream));
-    const int n_pad = (rows * cols + 3) & ~3;
-    const size_t smem = (size_t)kBatchPerWarp * (n_pad + kBatchGroup) * sizeof(float);
+    CU(h->batch_ctrl.ensure(sizeof(BatchCtrl)));
+    P.ctl = h->batch_ctrl.as<BatchCtrl>();
+    P.status = &P.ctl->status;
+    // B200LSAP_BATCH_CAP / B200LSAP_BATCH_CHUNK: developer A/B knobs of the filtered kernel
+    static const int cap_env = getenv("B200LSAP_BATCH_CAP") ? atoi(getenv("B200LSAP_BATCH_CAP")) : 0;
+    static const int chunk_env = getenv("B200LSAP_BATCH_CHUNK") ? atoi(getenv("B200LSAP_BATCH_CHUNK")) : 0;
+    P.cap = o.batch_bid_cap > 0 ? o.batch_bid_cap : (o.batch_bid_cap < 0 ? 0x7fffffff : (cap_env > 0 ? cap_env : 96));
+    P.chunk = chunk_env > 0 ? chunk_env : 16;
+    CU(cudaMemsetAsync(P.ctl, 0, sizeof(BatchCtrl), h->stream));
     using BatchKernel = void (*)(BatchParams);
-    static const BatchKernel kernels[kBatchColsPerLane] = {k_auction_batch<1>, k_auction_batch<2>, k_auction_batch<3>,
-                                                          k_auction_batch<4>, k_auction_batch<5>, k_auction_batch<6>,
-                                                          k_auction_batch<7>, k_auction_batch<8>};
-    const BatchKernel kernel = kernels[(cols + kBatchGroup - 1) / kBatchGroup - 1];
-    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32, smem));
-    if (per_sm < 1)
-        return fail(h, B200LSAP_ERR_SHAPE, "batched problem does not fit in shared memory");
-    int64_t grid = (batch + kBatchPerWarp - 1) / kBatchPerWarp;
-    const int64_t resident = (int64_t)per_sm * h->num_sms;
-    if (grid > resident)
-        grid = resident;
     // B200LSAP_BATCH_SMEM=1: the shared-memory kernel (k_auction_batch); B200LSAP_BATCH_WARPS=16|24|32: warps per
     // SM the streaming kernel is compiled for (developer A/B knobs)
     static const bool smem_mode = getenv("B200LSAP_BATCH_SMEM") && atoi(getenv("B200LSAP_BATCH_SMEM")) != 0;
@@ -1000,7 +1014,7 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     CU(cudaEventRecord(h->ev[1], h->stream));
     if (!smem_mode && filter_mode && cols % 4 == 0 && ((uintptr_t)a_dev_row_major & 15) == 0)
     {
-        // 16 problems per warp, four warps per CTA, one resident wave; a warp takes a slice of the batch
+        // 16 problems per warp, four warps per CTA, one resident wave; warps reserve problems from one counter
         constexpr int kFW = 4, kFC = 4;
 #define B200LSAP_FILTER(M) k_auction_batch_filter<M, true, kFW, kFC>, k_auction_batch_filter<M, false, kFW, kFC>
         static const BatchKernel kf[16] = {B200LSAP_FILTER(1), B200LSAP_FILTER(2), B200LSAP_FILTER(3),
@@ -1009,9 +1023,10 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
         const int kM = (cols + 7) / 8;
         const BatchKernel fk = kf[2 * (kM - 1) + (cols % 8 == 0 ? 0 : 1)];
         const size_t fsmem = kFW * batch_filter_warp_bytes(kM);
-        CU(cudaFuncSetAttribute(fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
         int fper_sm = 0;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fper_sm, fk, kFW * 32, fsmem));
+        int rc = batch_occupancy(h, (const void*)fk, kFW * 32, fsmem, fper_sm);
+        if (rc)
+            return rc;
         if (fper_sm < 1)
             return fail(h, B200LSAP_ERR_CUDA, "k_auction_batch_filter does not fit on an SM");
         int64_t fgrid = std::min<int64_t>((batch + 16 * kFW - 1) / (16 * kFW), (int64_t)fper_sm * h->num_sms);
@@ -1051,10 +1066,27 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
         }
     }
     else
+    {
+        const int n_pad = (rows * cols + 3) & ~3;
+        const size_t smem = (size_t)kBatchPerWarp * (n_pad + kBatchGroup) * sizeof(float);
+        static const BatchKernel kernels[kBatchColsPerLane] = {k_auction_batch<1>, k_auction_batch<2>, k_auction_batch<3>,
+                                                              k_auction_batch<4>, k_auction_batch<5>, k_auction_batch<6>,
+                                                              k_auction_batch<7>, k_auction_batch<8>};
+        const BatchKernel kernel = kernels[(cols + kBatchGroup - 1) / kBatchGroup - 1];
+        int per_sm = 0;
+        int rc = batch_occupancy(h, (const void*)kernel, 32, smem, per_sm);
+        if (rc)
+            return rc;
+        if (per_sm < 1)
+            return fail(h, B200LSAP_ERR_SHAPE, "batched problem does not fit in shared memory");
+        const int64_t grid = std::min<int64_t>((batch + kBatchPerWarp - 1) / kBatchPerWarp, (int64_t)per_sm * h->num_sms);
         kernel<<<(int)grid, 32, smem, h->stream>>>(P);
+    }
     h->launches++;
     CU(cudaEventRecord(h->ev[2], h->stream));
-    CU(cudaMemcpyAsync(&h->h_ctrl->status, P.status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(h->h_bctrl, P.ctl, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, h->stream));
+    if (!sync)
+        return B200LSAP_OK; // the caller synchronises and calls finish_batch
     CU(cudaStreamSynchronize(h->stream));
     CU(cudaGetLastError());
     if (stats)
@@ -1065,9 +1097,11 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
         stats->eps_final = P.eps;
         stats->bid_bytes = batch * ((int64_t)rows * cols * 4 + rows * 4);
         stats->launches = h->launches;
+        stats->batch_takeovers = h->h_bctrl->takeovers;
+        stats->batch_max_bids = h->h_bctrl->max_bids;
     }
-    if (h->h_ctrl->status != 0)
-        return fail(h, h->h_ctrl->status, b200lsap_status_string(h->h_ctrl->status));
+    if (h->h_bctrl->status != 0)
+        return fail(h, h->h_bctrl->status, b200lsap_status_string(h->h_bctrl->status));
     return B200LSAP_OK;
 }
 

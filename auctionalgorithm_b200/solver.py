@@ -62,7 +62,7 @@ class Handle:
 
     @staticmethod
     def _opts(eps_multiplier=None, eps_scaling=None, eps_start=None, eps_factor=None, max_rounds=None,
-              driver=None, tail_rows=None, narrow_rows=None, row_cache=None) -> Options:
+              driver=None, tail_rows=None, narrow_rows=None, row_cache=None, batch_bid_cap=None) -> Options:
         o = Options()
         _capi.lib().b200lsap_options_default(C.byref(o))
         if eps_multiplier is not None:
@@ -83,6 +83,8 @@ class Handle:
             o.tail_rows = tail_rows
         if narrow_rows is not None:
             o.narrow_rows = narrow_rows
+        if batch_bid_cap is not None:
+            o.batch_bid_cap = batch_bid_cap
         return o
 
     def set_stream(self, cuda_stream: int):

@@ -133,6 +133,104 @@ def test_filtered_batch_large_batch_is_consistent(handle, oracle_lib):
     assert torch.equal(out, out2)
 
 
+# ---- bid cap and whole-warp takeover (batch_warp_finish), dynamic hand-out ------------------------------------
+def _oracle_bids(oracle_lib, a):
+    return [oracle_lib.oracle_solve(p.astype(np.float64))["stats"]["bids"] for p in a]
+
+
+def test_filtered_batch_long_price_wars_of_the_bench_shards(handle, oracle_lib):
+    # the two slowest problems of the bench's seed-1 shards (1483 and 2148 bids; the mean is 44) among neighbours:
+    # they reach the default cap of 96 bids and are finished by a whole warp, continuing the same sweep
+    ids = [1117884, 3097078, 274277, 3248947] + list(range(1117884 - 20, 1117884 + 20))
+    a = np.stack([oracle_lib.generate(32, 48, 1, problem=i) for i in ids])
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    got = handle.solve_batch(a)
+    assert np.array_equal(got, ref)
+    bids = _oracle_bids(oracle_lib, a[:4])
+    assert bids[0] == 1483 and bids[1] == 2148
+    st = handle.last_stats
+    assert st["batch_max_bids"] == 2148 and st["batch_takeovers"] >= 4
+    # without the cap: same answer from the two-lane pass alone
+    assert np.array_equal(handle.solve_batch(a, batch_bid_cap=-1), ref)
+    assert handle.last_stats["batch_takeovers"] == 0 and handle.last_stats["batch_max_bids"] == 2148
+
+
+@pytest.mark.parametrize("shape", [(32, 48), (8, 12), (32, 64), (20, 44), (31, 36), (5, 8), (1, 4)])
+@pytest.mark.parametrize("cap", [1, 8])
+def test_filtered_batch_takeover_forced(handle, oracle_lib, shape, cap):
+    # a cap of 8 (or 1) bids sends every problem through the takeover after its first bids: the warp must continue
+    # exactly where the two lanes stopped, for every shape (half last chunks, fewer than 32 / more than 32 columns)
+    rows, cols = shape
+    for batch in (1, 40, 700):
+        a = _batch_inputs(oracle_lib, batch, rows, cols, 31)
+        ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+        assert failed == 0
+        assert np.array_equal(handle.solve_batch(a, batch_bid_cap=cap), ref)
+        if rows > cap:
+            assert handle.last_stats["batch_takeovers"] == batch
+
+
+def test_filtered_batch_takeover_with_zeros_ties_and_single_edges(handle, oracle_lib):
+    rng = np.random.default_rng(11)
+    a = _batch_inputs(oracle_lib, 500, 16, 24, 23)
+    a[rng.random(a.shape) < 0.7] = 0.0
+    for r in range(16):
+        a[:, r, r] = np.maximum(a[:, r, r], 0.05)
+    a[::3, 0, 1:] = 0.0                                  # single-edge rows: second best = -1e6
+    a[100:200] = (np.ceil(a[100:200] * 4) / 4).astype(np.float32)   # coarse grid: ties everywhere
+    for r in range(16):
+        a[100:200, r, r] = np.maximum(a[100:200, r, r], 0.25)
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    for cap in (2, 5, 0):
+        assert np.array_equal(handle.solve_batch(a, batch_bid_cap=cap), ref)
+
+
+def test_filtered_batch_synthetic_price_war(handle, oracle_lib):
+    # k + 1 rows whose k best columns coincide with equal values, every other column delta lower: the rows outbid
+    # each other in steps of eps until the prices have risen by delta, about k * delta / eps bids (30 000 here)
+    rows, cols, k = 32, 48, 4
+    eps = 1e-5 / cols
+    a = _batch_inputs(oracle_lib, 24, rows, cols, 41) * np.float32(0.5)
+    delta = np.float32(50000 * eps / (k + 1))
+    for b in range(24):
+        a[b, :k + 1, :] = np.float32(0.9) - delta
+        a[b, :k + 1, 7:7 + k] = np.float32(0.9)
+        a[b, k + 1:, 7:7 + k] = np.float32(0.001)       # the other rows stay out of the war
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    bids = _oracle_bids(oracle_lib, a[:1])[0]
+    assert 20000 < bids < 200000
+    got = handle.solve_batch(a)
+    assert np.array_equal(got, ref)
+    assert handle.last_stats["batch_max_bids"] >= bids and handle.last_stats["batch_takeovers"] == 24
+    # the watchdog still counts across the takeover
+    import auctionalgorithm_b200 as ab
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve_batch(a, max_rounds=5000)
+    assert e.value.status == ab.ERR_MAX_ROUNDS
+
+
+@pytest.mark.parametrize("batch", [1, 2, 16, 17, 63, 64, 65, 1000, 4099, 37889, 80000])
+def test_filtered_batch_dynamic_handout_covers_every_problem(handle, oracle_lib, batch):
+    # reservations of 16 problems from one counter: every problem solved exactly once whatever the batch size
+    # (partial last reservation, fewer problems than warps, more than one resident wave)
+    import torch
+    t = torch.empty((batch, 32, 48), dtype=torch.float32, device="cuda")
+    handle.generate_device(t.data_ptr(), batch, 32, 48, 48, 1, seed=7, problem0=5)
+    out = torch.full((batch, 32), -7, dtype=torch.int32, device="cuda")
+    handle.solve_batch_device(t.data_ptr(), batch, 32, 48, out.data_ptr())
+    got = out.cpu().numpy()
+    s = np.sort(got, axis=1)
+    assert got.min() >= 0 and got.max() < 48 and (s[:, 1:] != s[:, :-1]).all()
+    idx = np.unique(np.concatenate([np.arange(0, min(batch, 40)), np.arange(max(0, batch - 40), batch),
+                                    np.arange(0, batch, 211)]))
+    a = np.stack([oracle_lib.generate(32, 48, 7, problem=5 + int(b)) for b in idx])
+    ref, failed = oracle_lib.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0 and np.array_equal(got[idx], ref)
+
+
 def test_batch_errors(handle):
     import auctionalgorithm_b200 as ab
     with pytest.raises(ab.B200LsapError) as e:

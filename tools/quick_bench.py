@@ -35,8 +35,29 @@ def batch(n, rows=32, cols=48, reps=3):
         best = min(best, st["ms_solve"])
     print(f"batch {n}x{rows}x{cols}: {best:.3f} ms -> {n/best/1e3:.1f} M problems/s, {st['bid_bytes']/best/1e6:.0f} GB/s", flush=True)
 
+def batch_shards(n=1 << 20, shards=8, reps=3, **opt):
+    """C3 on the eight shards bench.py hands to ranks 0..7 (problem0 = k * n): a lucky shard cannot be the number."""
+    t = torch.empty((n, 32, 48), dtype=torch.float32, device="cuda")
+    out = torch.empty((n, 32), dtype=torch.int32, device="cuda")
+    res = []
+    for k in range(shards):
+        h.generate_device(t.data_ptr(), n, 32, 48, 48, 1, 1, problem0=k * n)
+        best = 1e9
+        for _ in range(reps):
+            st = h.solve_batch_device(t.data_ptr(), n, 32, 48, out.data_ptr(), **opt)
+            best = min(best, st["ms_solve"])
+        res.append(best)
+        print(f"shard {k} {opt}: {best:.3f} ms -> {n/best/1e3:.1f} M problems/s, takeovers {st['batch_takeovers']}, "
+              f"max bids {st['batch_max_bids']}", flush=True)
+    print(f"shards {opt}: best {min(res):.3f} worst {max(res):.3f} ms (worst/best {max(res)/min(res):.3f})", flush=True)
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["c1", "c2", "c3", "sq"]
+    if "c3shards" in which:
+        batch_shards()
+    if "c3caps" in which:
+        for cap in (-1, 64, 96, 128, 192):
+            batch_shards(shards=3, batch_bid_cap=cap)
     if "c1" in which: dense(200, 300)
     if "c2" in which: dense(2048, 3072)
     if "c3" in which: batch(1 << 16); batch(1 << 20)

@@ -1,4 +1,4 @@
-"""Small solves that reach every kernel variant, for compute-sanitizer (tools/gpu_sanitize.sh)."""
+"""Small solves that reach every kernel variant, for compute-sanitizer (tools/gpu.sh sanitize)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))

@@ -34,6 +34,8 @@ struct BatchCtrl
     int takeovers;           // problems that reached the bid cap and were finished by a whole warp
     int max_bids;            // largest bid count of a problem in this launch
     int pad;
+    unsigned long long hits, misses; // takeover bids answered from a row cache / by a full scan
+    unsigned long long dbg[4];       // -DB200LSAP_TIMING: cycles of the takeover's sections
 };
 
 struct BatchParams
@@ -550,10 +552,11 @@ __device__ __forceinline__ float filter_bound(float k, float pmax)
 // row -> column (or -1 everywhere and *status on failure); returns the final bid count.
 __device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_off, unsigned p64_off, unsigned p32_off,
                                               const float* __restrict__ A, int* __restrict__ out, int rows, int cols,
-                                              double eps, int max_bids, int* status, unsigned unassigned, unsigned todo,
+                                              double eps, int max_bids, BatchCtrl* ctl, unsigned unassigned, unsigned todo,
                                               int bids, float pmax)
 {
     extern __shared__ __align__(16) unsigned char batch_smem[];
+    int* status = &ctl->status;
     float* sA = reinterpret_cast<float*>(batch_smem + rows_off);
     signed char* ownc = reinterpret_cast<signed char*>(batch_smem + own_off);   // owner of a column (stays as it is)
     double* pc_lo = reinterpret_cast<double*>(batch_smem + p64_off);            // price of columns 0..31
@@ -576,39 +579,61 @@ __device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_of
             pc_hi[cB] = pB;
     }
     // this lane's row: cached columns (ascending, one per byte), their coefficients, bound of everything else
-    unsigned cc = 0;
+    unsigned cc = 0, pa01 = (p64_off >> 3) * 0x10001u, pa23 = pa01; // double index (a CTA's arrays may exceed 64 KB)
     double ca0 = 0.0, ca1 = 0.0, ca2 = 0.0, ca3 = 0.0;
     double cbound = CUDART_INF; // no cache yet: every bid misses
-    int fail = 0;
+#ifdef B200LSAP_TIMING
+    unsigned bt_acc[4] = {0, 0, 0, 0}, bt_t = clock();
+#define BT_TICK(k, ...)                                                                                            \
+    do                                                                                                             \
+    {                                                                                                              \
+        asm volatile("" ::__VA_ARGS__ : "memory");                                                                 \
+        const unsigned now_ = clock();                                                                             \
+        bt_acc[k] += now_ - bt_t;                                                                                  \
+        bt_t = now_;                                                                                               \
+    } while (0)
+#else
+#define BT_TICK(k, ...)
+#endif
+    int fail = 0, n_miss = 0;
+    const int bids_in = bids;
     while (unassigned != 0)
     {
         if (todo == 0)
             todo = unassigned; // next forward sweep (Auction.h:66-68, :220)
         const int i = __ffs(todo) - 1;
         todo &= todo - 1;
+        BT_TICK(3, "r"(i));
         __syncwarp(); // the previous bid's price and owner are visible
         // every lane evaluates its own row's cache (one instruction stream); lane i's answer is the bid
         int j, prev;
         double bid;
         {
+            // (shared-memory addresses of the cached columns' prices were formed when the cache was built)
+            const double* sm64 = reinterpret_cast<const double*>(batch_smem);
+            const double d0 = ca0 - sm64[pa01 & 0xffffu], d1 = ca1 - sm64[pa01 >> 16], d2 = ca2 - sm64[pa23 & 0xffffu],
+                         d3 = ca3 - sm64[pa23 >> 16];
             const int c0 = cc & 63, c1 = (cc >> 8) & 63, c2 = (cc >> 16) & 63, c3 = cc >> 24;
-            const double d0 = ca0 - *pc(c0), d1 = ca1 - *pc(c1), d2 = ca2 - *pc(c2), d3 = ca3 - *pc(c3);
             const int o0 = ownc[c0], o1 = ownc[c1], o2 = ownc[c2], o3 = ownc[c3];
             // strict '>' in ascending column order keeps the lowest column among equals (Auction.h:136)
             const bool g01 = d1 > d0, g23 = d3 > d2;
             const double vA = g01 ? d1 : d0, wA = g01 ? d0 : d1, vB = g23 ? d3 : d2, wB = g23 ? d2 : d3;
             const bool gB = vB > vA;
-            const double w = gB ? fmax(vA, wB) : fmax(vB, wA); // second best, may equal the best (Auction.h:147-148)
+            const double x2 = gB ? vA : vB, y2 = gB ? wB : wA;
+            const double w = x2 > y2 ? x2 : y2; // second best, may equal the best (Auction.h:147-148)
             const double aj = gB ? (g23 ? ca3 : ca2) : (g01 ? ca1 : ca0);
             const int mj = gB ? (g23 ? c3 : c2) : (g01 ? c1 : c0);
             const int mo = gB ? (g23 ? o3 : o2) : (g01 ? o1 : o0);
             const bool hit = w > cbound;
+            BT_TICK(0, "d"(w), "r"(mj), "r"(mo));
             j = __shfl_sync(kFullMask, hit ? mj : -1, i);
             prev = __shfl_sync(kFullMask, mo, i);
             bid = __shfl_sync(kFullMask, aj - w + eps, i); // Auction.h:250
+            BT_TICK(1, "d"(bid), "r"(j), "r"(prev));
         }
         if (j < 0)
         {
+            n_miss++;
             // full scan of row i, every lane two columns
             const float* row = sA + i * cols;
             const float a0 = hasA ? row[cA] : 0.f, a1 = hasB ? row[cB] : 0.f; // 0: no edge (Auction.h:134)
@@ -675,6 +700,9 @@ __device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_of
             if (lane == i)
             {
                 cc = (unsigned)c1 | ((unsigned)c2 << 8) | ((unsigned)c3 << 16) | ((unsigned)c4 << 24);
+                const unsigned lo_idx = p64_off >> 3, hi_idx = (p32_off >> 3) - 32u;
+                pa01 = ((c1 < 32 ? lo_idx : hi_idx) + c1) | (((c2 < 32 ? lo_idx : hi_idx) + c2) << 16);
+                pa23 = ((c3 < 32 ? lo_idx : hi_idx) + c3) | (((c4 < 32 ? lo_idx : hi_idx) + c4) << 16);
                 // a column without an edge can neither win nor be second: its value sinks below every bound
                 ca0 = f1 != 0.f ? (double)f1 : -1e300;
                 ca1 = f2 != 0.f ? (double)f2 : -1e300;
@@ -702,7 +730,13 @@ __device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_of
             fail = 3;
             break;
         }
+        BT_TICK(2, "r"(unassigned), "r"(todo));
     }
+#ifdef B200LSAP_TIMING
+    if (lane == 0)
+        for (int k = 0; k < 4; k++)
+            atomicAdd(&ctl->dbg[k], (unsigned long long)bt_acc[k]);
+#endif
     __syncwarp();
     if (fail)
     {
@@ -718,6 +752,11 @@ __device__ __noinline__ int batch_warp_finish(unsigned rows_off, unsigned own_of
             out[oA] = cA;
         if (oB >= 0)
             out[oB] = cB;
+    }
+    if (lane == 0)
+    {
+        atomicAdd(&ctl->misses, (unsigned long long)n_miss);
+        atomicAdd(&ctl->hits, (unsigned long long)(bids - bids_in - n_miss));
     }
     __syncwarp();
     return bids;
@@ -880,7 +919,9 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
                 break;
         }
 
-        // a problem that has reached the bid cap is finished by the whole warp (batch_warp_finish)
+        // a problem that has reached the bid cap is finished by the whole warp (batch_warp_finish).  (Also handing over
+        // a warp's last one or two problems once the batch has run dry was measured: 2 % slower, the takeovers' cold
+        // caches cost more than the idle lanes.)
         const unsigned cm = __ballot_sync(kFullMask, unassigned != 0 && bids >= P.cap);
         if (cm != 0)
         {
@@ -896,7 +937,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) k_auction_batch_filte
             const int total = batch_warp_finish(
                 wb_off + 16 * s32 * 4, wb_off + 3 * 16 * s32 * 4 + 16 * kBatchMaxRows * 8 + tg * kC8,
                 wb_off + 3 * 16 * s32 * 4 + tg * kBatchMaxRows * 8, wb_off + tg * s32 * 4, P.a + t_pb * n,
-                P.row2col + t_pb * P.rows, P.rows, P.cols, P.eps, P.max_bids, P.status, t_un, t_todo, t_bids, t_pmax);
+                P.row2col + t_pb * P.rows, P.rows, P.cols, P.eps, P.max_bids, P.ctl, t_un, t_todo, t_bids, t_pmax);
             if (lane == 0)
                 atomicAdd(&P.ctl->takeovers, 1);
             max_seen = max(max_seen, total);

@@ -1099,6 +1099,10 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
         stats->launches = h->launches;
         stats->batch_takeovers = h->h_bctrl->takeovers;
         stats->batch_max_bids = h->h_bctrl->max_bids;
+        stats->cache_hits = (int64_t)h->h_bctrl->hits;     // takeover bids answered from a row cache
+        stats->cache_misses = (int64_t)h->h_bctrl->misses; // ... by a full scan of the row
+        for (int k = 0; k < 4; k++)
+            h->h_ctrl->dbg[k] = (long long)h->h_bctrl->dbg[k]; // b200lsap_debug_counters
     }
     if (h->h_bctrl->status != 0)
         return fail(h, h->h_bctrl->status, b200lsap_status_string(h->h_bctrl->status));

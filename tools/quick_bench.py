@@ -48,13 +48,35 @@ def batch_shards(n=1 << 20, shards=8, reps=3, **opt):
             best = min(best, st["ms_solve"])
         res.append(best)
         print(f"shard {k} {opt}: {best:.3f} ms -> {n/best/1e3:.1f} M problems/s, takeovers {st['batch_takeovers']}, "
-              f"max bids {st['batch_max_bids']}", flush=True)
+              f"max bids {st['batch_max_bids']}, takeover hits/misses {st['cache_hits']}/{st['cache_misses']}", flush=True)
     print(f"shards {opt}: best {min(res):.3f} worst {max(res):.3f} ms (worst/best {max(res)/min(res):.3f})", flush=True)
 
 if __name__ == "__main__":
     which = sys.argv[1:] or ["c1", "c2", "c3", "sq"]
     if "c3shards" in which:
         batch_shards()
+    if "monster" in which:   # the slowest problems of the bench shards alone: takeover cost per bid
+        for pid in (3097078, 1117884, 3248947):
+            t = torch.empty((1, 32, 48), dtype=torch.float32, device="cuda")
+            out = torch.empty((1, 32), dtype=torch.int32, device="cuda")
+            h.generate_device(t.data_ptr(), 1, 32, 48, 48, 1, 1, problem0=pid)
+            for cap in (96, -1):
+                best = 1e9
+                for _ in range(5):
+                    st = h.solve_batch_device(t.data_ptr(), 1, 32, 48, out.data_ptr(), batch_bid_cap=cap)
+                    best = min(best, st["ms_solve"])
+                print(f"problem {pid} cap {cap}: {best*1e3:.1f} us, bids {st['batch_max_bids']}, hits/misses "
+                      f"{st['cache_hits']}/{st['cache_misses']} -> {best*1e3/st['batch_max_bids']:.3f} us/bid", flush=True)
+                dbg = h.debug_counters()
+                if any(dbg[:4]):
+                    print("   takeover cycles [eval, shfl, update, next-row]:", dbg[:4], flush=True)
+    if "monster1" in which:  # one launch of the slowest problem alone (ncu source-level profile of the takeover)
+        t = torch.empty((1, 32, 48), dtype=torch.float32, device="cuda")
+        out = torch.empty((1, 32), dtype=torch.int32, device="cuda")
+        h.generate_device(t.data_ptr(), 1, 32, 48, 48, 1, 1, problem0=3097078)
+        for _ in range(3):
+            st = h.solve_batch_device(t.data_ptr(), 1, 32, 48, out.data_ptr())
+        print(f"monster alone: {st['ms_solve']*1e3:.1f} us", flush=True)
     if "c3caps" in which:
         for cap in (-1, 64, 96, 128, 192):
             batch_shards(shards=3, batch_bid_cap=cap)

@@ -10,6 +10,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200LSAP_LIB") or os.path.join(PKG, "libb200lsap.so")
 
 COL_MAJOR, ROW_MAJOR = 0, 1
+IPC_HANDLE_BYTES = 64
 OK, ERR_SHAPE, ERR_INFEASIBLE, ERR_MAX_ROUNDS, ERR_CUDA, ERR_ARG, ERR_NO_DEVICE = range(7)
 
 
@@ -70,6 +71,14 @@ SIGNATURES = {
     "b200lsap_shard_resolve": (C.c_int, [_H, _P, C.c_int, C.POINTER(_i64)]),
     "b200lsap_shard_next_phase": (C.c_int, [_H, C.POINTER(C.c_int)]),
     "b200lsap_shard_finish": (C.c_int, [_H, _P, _P, C.POINTER(Stats)]),
+    "b200lsap_shard_comm_create": (C.c_int, [_H, _i64, C.c_int, _P]),
+    "b200lsap_shard_comm_ptr": (C.c_void_p, [_H]),
+    "b200lsap_shard_comm_connect": (C.c_int, [_H, C.c_int, C.c_int, _P, _P, C.c_int]),
+    "b200lsap_shard_reserve": (C.c_int, [_H, _i64, _i64]),
+    "b200lsap_solve_sharded_begin_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.POINTER(Options)]),
+    "b200lsap_solve_sharded_end": (C.c_int, [_H, _P, _P, C.POINTER(Stats)]),
+    "b200lsap_solve_sharded_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.POINTER(Options), _P, _P,
+                                                    C.POINTER(Stats)]),
     "b200lsap_debug_counters": (C.c_int, [_H, C.POINTER(_i64), C.c_int]),
     "b200lsap_host_alloc": (C.c_void_p, [_i64]),
     "b200lsap_host_free": (None, [_P]),

@@ -83,6 +83,19 @@ struct b200lsap_handle
         int64_t n = 0, rounds = 0, bids = 0, max_rounds = 0;
         int grid = 0;
     } sh;
+    // fused sharded solve (b200lsap_shard_comm_* / b200lsap_solve_sharded_*): this rank's mailbox and its peers'
+    struct
+    {
+        DevBuf box;
+        ShardComm cm{};
+        bool connected = false;
+        int share = 1;                 // ranks that run on this GPU (tests: several shards on one device)
+        std::vector<void*> opened;     // CUDA IPC mappings of the peers' mailboxes
+        bool running = false;
+        int64_t rows = 0, cols_global = 0, cols_local = 0;
+        double eps_final = 0;
+        int phases = 0;
+    } fused;
 };
 
 namespace
@@ -217,6 +230,9 @@ int b200lsap_destroy(b200lsap_handle* h)
                       &h->bid_val, &h->list0, &h->list1, &h->partial, &h->arrive, &h->ctrl, &h->out64, &h->batch_in,
                       &h->batch_out, &h->batch_ctrl})
         b->release();
+    for (void* p : h->fused.opened)
+        cudaIpcCloseMemHandle(p);
+    h->fused.box.release();
     for (auto& e : h->ev)
         if (e)
             cudaEventDestroy(e);
@@ -1475,3 +1491,232 @@ int b200lsap_shard_finish(b200lsap_handle* h, int32_t* row_to_col_dev, double* p
 }
 
 } // extern "C"
+
+// =============================================================================================
+// Fused column-sharded solve: one persistent cooperative kernel per rank, the per-round exchange inside the kernel
+// (peer stores into every rank's mailbox + flags, shard_kernels.cuh).  The caller only wires the mailboxes once.
+// =============================================================================================
+extern "C" {
+
+int b200lsap_shard_comm_create(b200lsap_handle* h, int64_t rows_cap, int n_ranks, void* ipc_handle_out)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (rows_cap < 1 || n_ranks < 1 || n_ranks > kShardMaxRanks)
+        return fail(h, B200LSAP_ERR_ARG, "shard_comm_create: need rows_cap >= 1 and 1 <= n_ranks <= 16");
+    CU(cudaSetDevice(h->device));
+    auto& f = h->fused;
+    for (void* p : f.opened)
+        cudaIpcCloseMemHandle(p);
+    f.opened.clear();
+    f.connected = false;
+    f.box.release(); // a fresh allocation: a new IPC handle, flags and epoch start from zero
+    const size_t bytes = kShardHeaderBytes + (size_t)2 * n_ranks * rows_cap * sizeof(ShardRec);
+    CU(f.box.ensure(bytes));
+    CU(cudaMemset(f.box.p, 0, bytes));
+    CU(cudaDeviceSynchronize());
+    f.cm = ShardComm{};
+    f.cm.n_ranks = n_ranks;
+    f.cm.rows_cap = rows_cap;
+    f.cm.spin_ns = 10ull * 1000 * 1000 * 1000;
+    if (const char* e = getenv("B200LSAP_SHARD_SPIN_MS"))
+        f.cm.spin_ns = (unsigned long long)std::max(1, atoi(e)) * 1000 * 1000;
+    if (ipc_handle_out)
+    {
+        static_assert(sizeof(cudaIpcMemHandle_t) == B200LSAP_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+        cudaIpcMemHandle_t ipc;
+        CU(cudaIpcGetMemHandle(&ipc, f.box.p));
+        memcpy(ipc_handle_out, &ipc, sizeof ipc);
+    }
+    return B200LSAP_OK;
+}
+
+void* b200lsap_shard_comm_ptr(b200lsap_handle* h) { return h ? h->fused.box.p : nullptr; }
+
+int b200lsap_shard_comm_connect(b200lsap_handle* h, int rank, int n_ranks, const void* ipc_handles,
+                                void* const* peer_ptrs, int ranks_on_this_device)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    auto& f = h->fused;
+    if (!f.box.p || n_ranks != f.cm.n_ranks || rank < 0 || rank >= n_ranks || ranks_on_this_device < 1)
+        return fail(h, B200LSAP_ERR_ARG, "shard_comm_connect: create the mailbox first, with the same n_ranks");
+    if (n_ranks > 1 && !ipc_handles && !peer_ptrs)
+        return fail(h, B200LSAP_ERR_ARG, "shard_comm_connect: need the peers' IPC handles or their pointers");
+    CU(cudaSetDevice(h->device));
+    f.cm.rank = rank;
+    f.share = ranks_on_this_device;
+    for (int q = 0; q < n_ranks; q++)
+    {
+        if (q == rank)
+        {
+            f.cm.box[q] = static_cast<unsigned char*>(f.box.p);
+            continue;
+        }
+        void* p = nullptr;
+        if (peer_ptrs && peer_ptrs[q])
+        {
+            // same process: the peer's own allocation; make its device reachable from ours
+            p = peer_ptrs[q];
+            cudaPointerAttributes at;
+            CU(cudaPointerGetAttributes(&at, p));
+            if (at.device != h->device)
+            {
+                int can = 0;
+                CU(cudaDeviceCanAccessPeer(&can, h->device, at.device));
+                if (!can)
+                    return fail(h, B200LSAP_ERR_CUDA, "shard_comm_connect: no peer access between the two devices");
+                const cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                    return fail(h, B200LSAP_ERR_CUDA, "cudaDeviceEnablePeerAccess", e);
+                cudaGetLastError();
+            }
+        }
+        else
+        {
+            cudaIpcMemHandle_t ipc;
+            memcpy(&ipc, static_cast<const unsigned char*>(ipc_handles) + (size_t)q * sizeof ipc, sizeof ipc);
+            CU(cudaIpcOpenMemHandle(&p, ipc, cudaIpcMemLazyEnablePeerAccess));
+            f.opened.push_back(p);
+        }
+        f.cm.box[q] = static_cast<unsigned char*>(p);
+    }
+    f.connected = true;
+    return B200LSAP_OK;
+}
+
+int b200lsap_shard_reserve(b200lsap_handle* h, int64_t rows, int64_t cols_global)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    if (rows < 1 || cols_global < rows || cols_global > 0x7fff0000ll)
+        return fail(h, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    CU(cudaSetDevice(h->device));
+    int grid = 0;
+    int rc = persistent_grid<float>(h, grid);
+    if (rc)
+        return rc;
+    return alloc_state<float>(h, rows, cols_global, round_up(cols_global, 32), grid * kWarpsPerBlock);
+}
+
+int b200lsap_solve_sharded_begin_f32(b200lsap_handle* h, const float* a_dev, int64_t rows, int64_t cols_local,
+                                     int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts)
+{
+    if (!h)
+        return B200LSAP_ERR_ARG;
+    auto& f = h->fused;
+    if (!f.connected)
+        return fail(h, B200LSAP_ERR_ARG, "sharded solve: the mailboxes are not connected (b200lsap_shard_comm_connect)");
+    if (!a_dev)
+        return fail(h, B200LSAP_ERR_ARG, "null pointer");
+    if (rows < 1 || cols_local < 1 || col0 < 0 || col0 + cols_local > cols_global || rows > cols_global ||
+        cols_global > 0x7fff0000ll || ld < round_up(cols_local, 4))
+        return fail(h, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    if (rows > f.cm.rows_cap)
+        return fail(h, B200LSAP_ERR_ARG, "sharded solve: more rows than the mailboxes were created for");
+    if (ld % 4 != 0 || col0 % 4 != 0 || ((uintptr_t)a_dev & 15) != 0)
+        return fail(h, B200LSAP_ERR_ARG,
+                    "a shard must be row-major, 16-byte aligned, with ld and col0 multiples of 4 (columns "
+                    "[cols_local, cols_local rounded up to 4) of every row zero)");
+    CU(cudaSetDevice(h->device));
+    DensePlan plan;
+    int rc = make_plan(h, rows, cols_global, opts, plan);
+    if (rc)
+        return rc;
+    int grid = 0;
+    rc = persistent_grid<float>(h, grid);
+    if (rc)
+        return rc;
+    grid = std::max(1, grid / f.share);
+    rc = alloc_state<float>(h, rows, cols_global, round_up(cols_global, 32), grid * kWarpsPerBlock);
+    if (rc)
+        return rc;
+    h->launches = 0;
+    auto& sh = h->sh; // shard_state's inputs
+    sh.A = a_dev;
+    sh.rows = rows;
+    sh.cols_local = cols_local;
+    sh.ld = ld;
+    sh.col0 = col0;
+    sh.cols_global = cols_global;
+    DenseState<float> g = shard_state(h, false), l = shard_state(h, true);
+    DenseCtrl* hc = h->h_ctrl;
+    memset(hc, 0, sizeof *hc);
+    hc->count[0] = (int)rows;
+    hc->n_phases = (int)plan.eps.size();
+    hc->max_rounds = plan.max_rounds;
+    for (size_t k = 0; k < plan.eps.size(); k++)
+        hc->eps[k] = plan.eps[k];
+    hc->eps_final = plan.eps.back();
+    CU(cudaMemcpyAsync(g.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    k_init<float><<<grid, kThreads, 0, h->stream>>>(g, 0);
+    k_absmax<float><<<grid_for(h, rows * (round_up(cols_local, 4) / 4), 256 * 8), 256, 0, h->stream>>>(l.A, l.ld, l.rows,
+                                                                                                      l.cols4, l.ctrl);
+    int c0 = (int)col0;
+    void* args[] = {(void*)&l, (void*)&g, (void*)&f.cm, (void*)&c0};
+    CU(cudaLaunchCooperativeKernel((void*)k_shard_persistent<float>, dim3(grid), dim3(kThreads), args, 0, h->stream));
+    h->launches += 3;
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaMemcpyAsync(h->h_ctrl, g.ctrl, sizeof(DenseCtrl), cudaMemcpyDeviceToHost, h->stream));
+    f.running = true;
+    f.rows = rows;
+    f.cols_global = cols_global;
+    f.cols_local = cols_local;
+    f.eps_final = plan.eps.back();
+    f.phases = (int)plan.eps.size();
+    return B200LSAP_OK;
+}
+
+int b200lsap_solve_sharded_end(b200lsap_handle* h, int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    if (!h || !h->fused.running)
+        return fail(h, B200LSAP_ERR_ARG, "no fused sharded solve in flight");
+    auto& f = h->fused;
+    CU(cudaSetDevice(h->device));
+    f.running = false;
+    if (row_to_col_dev)
+        CU(cudaMemcpyAsync(row_to_col_dev, h->row2col.p, f.rows * sizeof(int32_t), cudaMemcpyDeviceToDevice, h->stream));
+    if (prices_dev)
+        CU(cudaMemcpyAsync(prices_dev, h->prices.p, f.cols_global * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    if (stats)
+    {
+        memset(stats, 0, sizeof *stats);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]);
+        stats->ms_solve = ms;
+        stats->rounds = h->h_ctrl->rounds;
+        stats->bids = h->h_ctrl->bids;
+        stats->phases = h->h_ctrl->phase + 1;
+        stats->bid_bytes = h->h_ctrl->bids * f.cols_local * (int64_t)sizeof(float);
+        stats->eps_final = f.eps_final;
+        stats->launches = h->launches;
+    }
+    h->last_cols = f.cols_global;
+    const int st = h->h_ctrl->status;
+    if (st != 0)
+    {
+        if (st == 4)
+        {
+            f.connected = false; // the flag counters of the ranks may have diverged: wire the mailboxes again
+            return fail(h, B200LSAP_ERR_CUDA, "sharded solve: a peer rank did not arrive at an exchange (spin limit)");
+        }
+        return fail(h, st, b200lsap_status_string(st));
+    }
+    return B200LSAP_OK;
+}
+
+int b200lsap_solve_sharded_device_f32(b200lsap_handle* h, const float* a_dev, int64_t rows, int64_t cols_local,
+                                      int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts,
+                                      int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats)
+{
+    const int rc = b200lsap_solve_sharded_begin_f32(h, a_dev, rows, cols_local, ld, col0, cols_global, opts);
+    if (rc)
+        return rc;
+    return b200lsap_solve_sharded_end(h, row_to_col_dev, prices_dev, stats);
+}
+
+} // extern "C"
+

@@ -186,4 +186,268 @@ __global__ void __launch_bounds__(1024) k_shard_compact(const int* __restrict__ 
         *count = total;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused form: the whole column-sharded solve in ONE persistent cooperative kernel per GPU, the
+// exchange written into the kernel (north_star (5): "per-round NVLink max-bid reduction").
+//
+// Every rank owns a MAILBOX in its own HBM: [2 buffers][n_ranks sources][rows] records of 32 bytes, and one
+// flag word per source.  Rank r's bid phase stores the record of bidding row i straight into slot
+// [round & 1][r][i] of EVERY rank's mailbox — peer stores over NVLink (cudaDeviceEnablePeerAccess in one process,
+// CUDA IPC mappings across the processes of a torchrun job), 32 bytes each, issued by the warp that completed the
+// row while the other warps still scan: the transfer overlaps the scan row by row.  A system-scope fence, one grid
+// sync, then the rank raises its flag in every mailbox (st.release.sys) and every CTA waits until the n_ranks
+// flags of its own mailbox show the round (ld.acquire.sys on local memory).  Merge (AuctionMT.h:377-398: exact
+// top-2 merge in interval = rank order), resolve and compaction then run on every rank's replica of the prices
+// and of the assignment, identically, so nobody has to agree on anything else: the number of bidders, the phase and
+// the end of the solve follow from the replicated state.  Records are addressed by ROW, so the replicas' bidder
+// lists need not be in the same order (the host-driven path above needs k_shard_compact for that).
+// Two buffers suffice: a rank can only write round t + 2 after it has seen every peer's flag of round t + 1, which
+// a peer raises after it has finished reading round t.
+// The host is not touched per round: 3 grid syncs and one flag exchange (~2 us over NVLink) per round.
+// Flags count exchanges monotonically across solves (the epoch lives in the mailbox header), so nothing is reset
+// between solves; a peer that never shows up ends the kernel through the spin limit with an error status instead
+// of hanging the GPU.
+// ---------------------------------------------------------------------------------------------
+constexpr int kShardMaxRanks = 16;
+constexpr int kShardHeaderBytes = 4096; // flags: rank q at byte 128 q; amax box at 2048 + 8 q; epoch at 3072
+
+struct ShardComm
+{
+    unsigned char* box[kShardMaxRanks]; // box[q]: base of rank q's mailbox (header + records); box[rank] is local
+    int rank, n_ranks;
+    long long rows_cap;                 // records per (buffer, source) in every mailbox
+    unsigned long long spin_ns;         // give up waiting for a peer after this long
+};
+
+__device__ __forceinline__ unsigned long long* shard_flag(const ShardComm& cm, int owner, int src)
+{
+    return reinterpret_cast<unsigned long long*>(cm.box[owner] + 128 * src);
+}
+__device__ __forceinline__ ShardRec* shard_slot(const ShardComm& cm, int owner, int buf, int src)
+{
+    return reinterpret_cast<ShardRec*>(cm.box[owner] + kShardHeaderBytes) + ((long long)buf * cm.n_ranks + src) * cm.rows_cap;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Raise this rank's flag in every mailbox (CTA 0, after a grid sync that follows every writer's system fence),
+// then wait in every CTA until all sources have raised theirs in the local mailbox.  Returns false in a CTA that
+// gave up (it has raised the status; the caller's next grid sync makes that visible to every CTA).
+__device__ __forceinline__ bool shard_exchange(const ShardComm& cm, unsigned long long value, int* status)
+{
+    __shared__ int timed_out;
+    if (threadIdx.x == 0)
+        timed_out = 0;
+    __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x < cm.n_ranks)
+        st_release_sys(shard_flag(cm, threadIdx.x, cm.rank), value);
+    if (threadIdx.x < cm.n_ranks)
+    {
+        const unsigned long long* f = shard_flag(cm, cm.rank, threadIdx.x);
+        const unsigned long long t0 = global_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(f) < value)
+        {
+            if ((++spins & 1023u) == 0 && (global_ns() - t0 > cm.spin_ns || *reinterpret_cast<volatile int*>(status) != 0))
+            {
+                timed_out = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    if (timed_out && threadIdx.x == 0)
+        atomicCAS(status, 0, 4); // B200LSAP_ERR_CUDA: a peer did not arrive
+    return timed_out == 0;
+}
+
+// l: the scan view (this rank's columns; prices / pricesf offset to its first column), g: the global view (all
+// columns; the replicated state).  Both share the controller block and the lists.
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_constant__ DenseState<T> l,
+                                                                   const __grid_constant__ DenseState<T> g,
+                                                                   const __grid_constant__ ShardComm cm, int col0)
+{
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31;
+    const int warp_global = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    const int total_warps = gridDim.x * kWarpsPerBlock;
+    const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+    const long long n_threads = (long long)gridDim.x * kThreads;
+    volatile DenseCtrl* ctrl = g.ctrl;
+    unsigned long long* epoch_p = reinterpret_cast<unsigned long long*>(cm.box[cm.rank] + 3072);
+    const unsigned long long epoch = *epoch_p;
+    unsigned long long x = 0; // exchanges of this solve so far
+
+    // max |a| over all shards (slack of the single-precision filter): every rank drops its own into every mailbox
+    if (tid < cm.n_ranks)
+        *reinterpret_cast<volatile double*>(cm.box[tid] + 2048 + 8 * cm.rank) = ctrl->amax;
+    __threadfence_system();
+    grid.sync();
+    shard_exchange(cm, epoch + ++x, &g.ctrl->status);
+    grid.sync();
+    bool alive = ctrl->status == 0; // uniform: read between two grid syncs
+    double amax = 0.0;
+    for (int q = 0; q < cm.n_ranks; q++)
+        amax = fmax(amax, __ldcg(reinterpret_cast<const double*>(cm.box[cm.rank] + 2048 + 8 * q)));
+
+    int cur = 0, phase = 0;
+    const int n_phases = ctrl->n_phases;
+    const long long max_rounds = ctrl->max_rounds;
+    long long rounds = 0, bids = 0;
+    double eps = ctrl->eps[0];
+    while (alive)
+    {
+        const int n = ctrl->count[cur];
+        if (n == 0)
+        {
+            if (phase + 1 >= n_phases)
+                break;
+            phase++;
+            eps = ctrl->eps[phase];
+            grid.sync(); // everybody has read count[cur] == 0 before it is overwritten
+            reset_phase(g, g.list[cur], tid, n_threads);
+            if (tid == 0)
+                ctrl->count[cur] = g.rows;
+            grid.sync();
+            continue;
+        }
+        if (rounds >= max_rounds)
+        {
+            if (tid == 0)
+                ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS (replicated state: every rank stops here)
+            break;
+        }
+        if (tid == 0)
+            ctrl->count[cur ^ 1] = 0;
+        const int buf = (int)(x & 1);
+        // ---- bid phase over this rank's columns: bid_phase's scan, the record goes to every mailbox -------------
+        {
+            const double pmax = fmax(ctrl->pmax, amax);
+            const float margin = filter_margin(amax, pmax);
+            const int* __restrict__ list = g.list[cur];
+            const int S = split_factor(n, total_warps, l.cols4, l.min_seg);
+            int seg = (l.cols4 + S - 1) / S;
+            seg = (seg + 127) & ~127;
+            const long long items = (long long)n * S;
+            for (long long item = warp_global; item < items; item += total_warps)
+            {
+                const int b = (int)(item / S), sg = (int)(item - (long long)b * S);
+                const int i = list[b];
+                const int c0 = sg * seg, c1 = min(c0 + seg, l.cols4);
+                Top2<T> t = scan_segment<T>(l, l.A + (long long)i * l.ld, margin, -INFINITY, c0, c1, lane);
+                top2_warp_reduce_sparse(t);
+                bool final_warp = S == 1;
+                if (S > 1)
+                {
+                    int ticket = 0;
+                    if (lane == 0)
+                    {
+                        l.partial[(long long)b * S + sg] = t;
+                        __threadfence();
+                        ticket = atomicAdd(&l.arrive[b], 1);
+                    }
+                    ticket = __shfl_sync(kFullMask, ticket, 0);
+                    if (ticket == S - 1)
+                    {
+                        __threadfence();
+                        Top2<T> m = top2_empty<T>();
+                        for (int k = lane; k < S; k += 32)
+                            top2_merge(m, top2_load_cg(&l.partial[(long long)b * S + k]));
+                        top2_warp_reduce(m);
+                        t = m;
+                        final_warp = true;
+                        if (lane == 0)
+                            l.arrive[b] = 0;
+                    }
+                }
+                if (final_warp && lane < cm.n_ranks)
+                {
+                    ShardRec r;
+                    r.v = t.v;
+                    r.w = t.w;
+                    r.a = (double)t.a;
+                    r.j = t.j >= 0 ? t.j + col0 : -1;
+                    r.row = i;
+                    shard_slot(cm, lane, buf, cm.rank)[i] = r; // lane q writes rank q's mailbox
+                }
+            }
+        }
+        __threadfence_system();
+        grid.sync();
+        // ---- every rank, identically: merge the ranks' records per bidder, place the bid on the replica ---------
+        if (shard_exchange(cm, epoch + ++x, &g.ctrl->status))
+        {
+            const double pmax = fmax(ctrl->pmax, amax);
+            const ShardRec* mine = shard_slot(cm, cm.rank, buf, 0);
+            for (long long b = tid; b < n; b += n_threads)
+            {
+                const int i = g.list[cur][b];
+                Top2<double> m;
+                m.v = m.w = -kNoSecondBest;
+                m.j = -1;
+                m.a = 0.0;
+                bool ok = true;
+                for (int r = 0; r < cm.n_ranks; r++)
+                {
+                    // (written by a peer during this kernel: L2 loads, never the non-coherent path)
+                    const double2* rp = reinterpret_cast<const double2*>(mine + r * cm.rows_cap + i);
+                    const double2 lo = __ldcg(rp), hi = __ldcg(rp + 1);
+                    Top2<double> o;
+                    o.v = lo.x;
+                    o.w = lo.y;
+                    o.a = hi.x;
+                    o.j = (int)(__double_as_longlong(hi.y) & 0xffffffffll);
+                    ok = ok && (int)(__double_as_longlong(hi.y) >> 32) == i;
+                    top2_merge(m, o);
+                }
+                if (!ok || m.j < 0)
+                {
+                    g.ctrl->status = ok ? 2 : 4; // infeasible row / a record that is not this row's
+                    g.bid_col[i] = -1;
+                    continue;
+                }
+                const double bid = m.a - m.w + eps; // Auction.h:250
+                g.bid_col[i] = m.j;
+                g.bid_val[i] = bid;
+                g.profits[i] = m.w - eps; // Auction.h:253
+                slot_offer(&g.slots[m.j], bid, i);
+                if (bid > pmax)
+                    atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->pmax), (unsigned long long)__double_as_longlong(bid));
+            }
+        }
+        grid.sync();
+        if (ctrl->status != 0)
+            break;
+        resolve_phase<T>(g, g.list[cur], n, g.list[cur ^ 1], &g.ctrl->count[cur ^ 1], tid, n_threads, lane);
+        grid.sync();
+        cur ^= 1;
+        rounds++;
+        bids += n;
+    }
+    if (tid == 0)
+    {
+        ctrl->rounds = rounds;
+        ctrl->bids = bids;
+        ctrl->phase = phase;
+        ctrl->cur = cur;
+        ctrl->done = 1;
+        *epoch_p = epoch + x;
+    }
+}
+
 } // namespace b200lsap

@@ -230,6 +230,46 @@ class Handle:
         self._check(rc)
         return self.last_stats
 
+    # ---- fused column-sharded solve: the exchange runs inside the kernel (include/b200lsap.h) ----
+    def shard_comm_create(self, rows_cap: int, n_ranks: int) -> bytes:
+        """Allocates this rank's mailbox; returns its CUDA IPC handle (64 bytes) for ranks in other processes."""
+        buf = C.create_string_buffer(_capi.IPC_HANDLE_BYTES)
+        self._check(self._lib.b200lsap_shard_comm_create(self._h, rows_cap, n_ranks, buf))
+        return buf.raw
+
+    def shard_comm_ptr(self) -> int:
+        return self._lib.b200lsap_shard_comm_ptr(self._h) or 0
+
+    def shard_comm_connect(self, rank: int, n_ranks: int, ipc_handles: Optional[bytes] = None,
+                           peer_ptrs: Optional[list] = None, ranks_on_this_device: int = 1):
+        ptrs = None
+        if peer_ptrs is not None:
+            ptrs = (C.c_void_p * n_ranks)(*[C.c_void_p(p) if p else None for p in peer_ptrs])
+        self._check(self._lib.b200lsap_shard_comm_connect(self._h, rank, n_ranks, ipc_handles, ptrs,
+                                                          ranks_on_this_device))
+
+    def shard_reserve(self, rows: int, cols_global: int):
+        self._check(self._lib.b200lsap_shard_reserve(self._h, rows, cols_global))
+
+    def solve_sharded_begin(self, a_ptr: int, rows: int, cols_local: int, ld: int, col0: int, cols_global: int,
+                            **options):
+        o = self._opts(**options)
+        self._check(self._lib.b200lsap_solve_sharded_begin_f32(self._h, C.c_void_p(a_ptr), rows, cols_local, ld, col0,
+                                                               cols_global, C.byref(o)))
+
+    def solve_sharded_end(self, r2c_ptr: int, prices_ptr: int = 0) -> dict:
+        st = Stats()
+        rc = self._lib.b200lsap_solve_sharded_end(self._h, C.c_void_p(r2c_ptr),
+                                                  C.c_void_p(prices_ptr) if prices_ptr else None, C.byref(st))
+        self.last_stats = st.as_dict()
+        self._check(rc)
+        return self.last_stats
+
+    def solve_sharded_device(self, a_ptr: int, rows: int, cols_local: int, ld: int, col0: int, cols_global: int,
+                             r2c_ptr: int, prices_ptr: int = 0, **options) -> dict:
+        self.solve_sharded_begin(a_ptr, rows, cols_local, ld, col0, cols_global, **options)
+        return self.solve_sharded_end(r2c_ptr, prices_ptr)
+
     def debug_counters(self):
         out = (C.c_int64 * 16)()
         self._check(self._lib.b200lsap_debug_counters(self._h, out, 16))

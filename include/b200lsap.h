@@ -230,6 +230,41 @@ int b200lsap_shard_next_phase(b200lsap_handle* handle, int* more);
 int b200lsap_shard_finish(b200lsap_handle* handle, int32_t* row_to_col_dev, double* prices_dev,
                           b200lsap_stats* stats);
 
+/*
+ * Fused form of the column-sharded solve: the whole solve is ONE persistent cooperative kernel per rank and the
+ * per-round exchange happens inside it — every rank stores its 32-byte records straight into every other rank's
+ * mailbox over NVLink (peer memory) and raises a flag there; merge and resolve run on every rank's replica.  The
+ * host is not touched per round and the library needs no communicator: the caller wires the mailboxes ONCE.
+ *     shard_comm_create   allocates this rank's mailbox for problems of up to rows_cap rows and n_ranks (<= 16)
+ *                         ranks; ipc_handle_out (nullable) receives its CUDA IPC handle (64 bytes)
+ *     shard_comm_connect  rank / n_ranks and, for every rank, EITHER its IPC handle (ipc_handles: n_ranks * 64
+ *                         bytes, rank-major; ranks in other processes, e.g. exchanged with an all-gather) OR its
+ *                         mailbox pointer (peer_ptrs[q] = b200lsap_shard_comm_ptr of rank q's handle; ranks in this
+ *                         process, peer access is enabled here).  ranks_on_this_device > 1 (tests: several shards
+ *                         on one GPU) divides the grid so that the ranks' kernels are resident together.
+ *     solve_sharded_device_f32   collective: every rank calls it with its shard (same layout rules as
+ *                         shard_begin_f32, ranks in increasing col0 order = rank order); returns this rank's
+ *                         replica of the assignment and of the prices.  _begin / _end split it so that one host
+ *                         thread can start every rank of a single-process run before it waits for any; such a
+ *                         caller first calls shard_reserve on every handle (device buffers for the problem size:
+ *                         growing them later would free memory, which waits for the kernels already running).
+ * A rank that never arrives ends the others with B200LSAP_ERR_CUDA after a spin limit (10 s; the mailboxes must
+ * then be wired again) instead of hanging the GPU.  Same rounds as the host-driven form above: identical prices.
+ */
+#define B200LSAP_IPC_HANDLE_BYTES 64
+int b200lsap_shard_comm_create(b200lsap_handle* handle, int64_t rows_cap, int n_ranks, void* ipc_handle_out);
+void* b200lsap_shard_comm_ptr(b200lsap_handle* handle);
+int b200lsap_shard_comm_connect(b200lsap_handle* handle, int rank, int n_ranks, const void* ipc_handles,
+                                void* const* peer_ptrs, int ranks_on_this_device);
+int b200lsap_shard_reserve(b200lsap_handle* handle, int64_t rows, int64_t cols_global);
+int b200lsap_solve_sharded_begin_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols_local,
+                                     int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts);
+int b200lsap_solve_sharded_end(b200lsap_handle* handle, int32_t* row_to_col_dev, double* prices_dev,
+                               b200lsap_stats* stats);
+int b200lsap_solve_sharded_device_f32(b200lsap_handle* handle, const float* a_dev, int64_t rows, int64_t cols_local,
+                                      int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts,
+                                      int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats);
+
 /* Full-sweep bidding pass for measurement: every row bids once, nothing is updated.
  * use_last_prices = 0: the state a solve starts from (zero prices, no candidate lists: the first
  * sweep of the first eps phase).  1: the state the handle's last dense solve left: its prices and,

@@ -212,6 +212,23 @@ def reference_solve_csr(values, row_ptr, col_idx, rows: int, cols: int):
     return dict(x=ex[:n].copy(), y=ey[:n].copy(), v=ev[:n].copy(), seconds=sec.value)
 
 
+def reference_batch(a: np.ndarray, n_threads: int = 1):
+    """The unmodified reference's Auction<double>::solve looped over a [batch, rows, cols] float32 array on
+    n_threads threads -> (row_to_col int32 [batch, rows], seconds)."""
+    lib = reference()
+    if lib is None or not hasattr(lib, "ref_auction_batch_f32_as_f64"):
+        raise RuntimeError("oracle/_ref/libref_auction.so lacks ref_auction_batch_f32_as_f64 (rebuild where /root/reference exists)")
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    batch, rows, cols = a.shape
+    out = np.full((batch, rows), -1, np.int32)
+    sec = C.c_double(0)
+    lib.ref_auction_batch_f32_as_f64.restype = C.c_int64
+    lib.ref_auction_batch_f32_as_f64.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                                 C.POINTER(C.c_double)]
+    lib.ref_auction_batch_f32_as_f64(a.ctypes.data, batch, rows, cols, n_threads, out.ctypes.data, C.byref(sec))
+    return out, sec.value
+
+
 def oracle_batch(a: np.ndarray, use_double: bool = True, n_threads: int = 1):
     """a: [batch, rows, cols] float32 C-contiguous -> (row_to_col int32 [batch, rows], failed)."""
     lib = oracle()

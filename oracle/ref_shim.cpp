@@ -17,6 +17,7 @@
 
 #include <cstdint>
 #include <cstring>
+#include <vector>
 
 namespace
 {
@@ -103,6 +104,38 @@ int64_t ref_auction_f32_as_f64(const float* a, int64_t rows, int64_t cols, int64
     if (seconds_out)
         *seconds_out = std::chrono::duration<double>(t1 - t0).count();
     return flatten<double>(edges, ex, ey, ev);
+}
+
+/* The reference has no batch API: Auction<double>::solve called once per problem, the problems
+ * split over n_threads std::threads (solve() is re-entrant: locals only).  a: batch contiguous row-major
+ * rows x cols fp32 problems, widened exactly to double per problem.  row_to_col[b*rows + i] = column of row i.
+ * seconds_out: wall time of the whole threaded loop (matrix fill + solve per problem). */
+int64_t ref_auction_batch_f32_as_f64(const float* a, int64_t batch, int rows, int cols, int n_threads,
+                                     int32_t* row_to_col, double* seconds_out)
+{
+    if (n_threads < 1)
+        n_threads = 1;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> pool;
+    for (int t = 0; t < n_threads; t++)
+        pool.emplace_back([=]() {
+            Mat<double> m(rows, cols);
+            for (int64_t b = batch * t / n_threads; b < batch * (t + 1) / n_threads; b++)
+            {
+                const float* p = a + b * (int64_t)rows * cols;
+                for (int i = 0; i < rows; i++)
+                    for (int j = 0; j < cols; j++)
+                        m(i, j) = (double)p[i * cols + j];
+                const auto edges = LSAP::Auction<double>::solve(m);
+                for (const auto& e : edges)
+                    row_to_col[b * rows + (int64_t)e.x] = (int32_t)e.y;
+            }
+        });
+    for (auto& th : pool)
+        th.join();
+    if (seconds_out)
+        *seconds_out = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return batch;
 }
 
 /* Auction<double, SparseMatrix<double, RowMajor>>::solve (the driver's second call, LSAP.cpp:36-38,51)

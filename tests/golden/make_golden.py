@@ -33,7 +33,8 @@ SMALL = [
     (100, 101, 1, False), (200, 300, 1, True), (200, 300, 2, True), (200, 300, 3, True), (200, 200, 1, False),
     (256, 256, 2, False), (511, 513, 1, False), (512, 768, 1, True), (1024, 1536, 1, True),
 ]
-BIG = [(2048, 3072, 1, True), (2048, 3072, 2, True), (2048, 2048, 1, False), (4096, 4096, 1, False)]
+BIG = [(2048, 3072, 1, True), (2048, 3072, 2, True), (2048, 2048, 1, False), (4096, 4096, 1, False),
+       (8192, 12288, 1, False)]   # the last one: the multi-GPU column-sharded test (tests/test_gpu_multi.py)
 C4 = [(16384, 16384, 1, False)]
 
 

@@ -399,6 +399,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.sweep_split = h->sweep_split;
     s.tail_rows = 0;
     s.dry = 0;
+    s.narrow_after = 0;
     return s;
 }
 
@@ -445,6 +446,11 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
     hc->phase_budget = eps_auto ? 4 * plan.rows + 1024 : 0;
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
     s.use_cache = (plan.driver == 0 && plan.use_cache) ? 1 : 0;
+    {
+        // the cache-building sweep reads the matrix once (~6.5 TB/s); a small wide round costs ~20 us
+        const double sweep_us = (double)plan.rows * (double)ld * sizeof(T) / 6.5e6;
+        s.narrow_after = sweep_us > 1000.0 ? (int)std::min(1e6, sweep_us / 20.0) : 0;
+    }
     std::vector<double> eps = plan.eps;
 
     CU(cudaEventRecord(h->ev[1], h->stream));
@@ -804,6 +810,27 @@ template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_init_csr(
     }
 }
 
+// Validation of device-resident CSR arrays (one thread per row): status 5 (bad arrays) wins over 2 (empty row).
+__global__ void __launch_bounds__(256) k_check_csr(const int* __restrict__ ptr, const int* __restrict__ col, long long rows,
+                                                   long long cols, long long nnz, int* status)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < rows; i += (long long)gridDim.x * blockDim.x)
+    {
+        const long long a = ptr[i], b = ptr[i + 1];
+        int bad = 0;
+        if ((i == 0 && a != 0) || (i == rows - 1 && b != nnz) || b < a || a < 0 || b > nnz)
+            bad = 5;
+        else if (b == a)
+            bad = 2;
+        else
+            for (long long k = a; k < b; k++)
+                if (col[k] < 0 || col[k] >= cols || (k > a && col[k] <= col[k - 1]))
+                    bad = 5;
+        if (bad)
+            atomicMax(status, bad);
+    }
+}
+
 template <typename T>
 int solve_csr(b200lsap_handle* h, const T* values, const int32_t* row_ptr, const int32_t* col_idx, int64_t rows,
               int64_t cols, int64_t nnz, bool on_host, const b200lsap_options* opts, void* row_to_col, double* prices_out,
@@ -821,9 +848,16 @@ int solve_csr(b200lsap_handle* h, const T* values, const int32_t* row_ptr, const
         if (row_ptr[0] != 0 || row_ptr[rows] != nnz)
             return fail(h, B200LSAP_ERR_ARG, "row_ptr[0] must be 0 and row_ptr[rows] must equal nnz");
         for (int64_t i = 0; i < rows; i++)
+        {
             if (row_ptr[i + 1] <= row_ptr[i])
                 return fail(h, row_ptr[i + 1] < row_ptr[i] ? B200LSAP_ERR_ARG : B200LSAP_ERR_INFEASIBLE,
                             row_ptr[i + 1] < row_ptr[i] ? "row_ptr is not monotone" : "a row without a stored entry");
+            // a column outside [0, cols) would index prices / owners / bid slots out of bounds on the device
+            for (int64_t k = row_ptr[i]; k < row_ptr[i + 1]; k++)
+                if (col_idx[k] < 0 || col_idx[k] >= cols || (k > row_ptr[i] && col_idx[k] <= col_idx[k - 1]))
+                    return fail(h, B200LSAP_ERR_ARG,
+                                "col_idx must lie in [0, cols) and ascend strictly inside a row (a compressed Eigen matrix)");
+        }
     }
     CU(cudaSetDevice(h->device));
     DensePlan plan;
@@ -853,6 +887,21 @@ int solve_csr(b200lsap_handle* h, const T* values, const int32_t* row_ptr, const
         m.ptr = row_ptr;
         m.col = col_idx;
         m.val = values;
+        // device arrays: the same checks as on the host path, before anything is indexed with them
+        CU(h->ctrl.ensure(sizeof(DenseCtrl)));
+        int* flag = &h->ctrl.as<DenseCtrl>()->status;
+        CU(cudaMemsetAsync(flag, 0, sizeof(int), h->stream));
+        k_check_csr<<<grid_for(h, rows, 256), 256, 0, h->stream>>>(row_ptr, col_idx, rows, cols, nnz, flag);
+        CU(cudaMemcpyAsync(&h->h_ctrl->status, flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        CU(cudaGetLastError());
+        h->launches++;
+        if (h->h_ctrl->status != 0)
+            return fail(h, h->h_ctrl->status,
+                        h->h_ctrl->status == B200LSAP_ERR_INFEASIBLE
+                            ? "a row without a stored entry"
+                            : "bad CSR arrays: row_ptr[0] == 0, row_ptr[rows] == nnz, row_ptr monotone, col_idx in [0, cols) "
+                              "ascending strictly inside a row");
     }
     // the arrays of a round (prices, owners, bid slots, bidder lists); no candidate lists or row caches
     CU(h->prices.ensure((cols + 512) * sizeof(double)));
@@ -1651,12 +1700,11 @@ int b200lsap_solve_sharded_begin_f32(b200lsap_handle* h, const float* a_dev, int
     CU(cudaMemcpyAsync(g.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
     CU(cudaEventRecord(h->ev[1], h->stream));
     k_init<float><<<grid, kThreads, 0, h->stream>>>(g, 0);
-    k_absmax<float><<<grid_for(h, rows * (round_up(cols_local, 4) / 4), 256 * 8), 256, 0, h->stream>>>(l.A, l.ld, l.rows,
-                                                                                                      l.cols4, l.ctrl);
+    // (no pass over the matrix for max |a|: the kernel takes it from its first sweep)
     int c0 = (int)col0;
     void* args[] = {(void*)&l, (void*)&g, (void*)&f.cm, (void*)&c0};
     CU(cudaLaunchCooperativeKernel((void*)k_shard_persistent<float>, dim3(grid), dim3(kThreads), args, 0, h->stream));
-    h->launches += 3;
+    h->launches += 2;
     CU(cudaEventRecord(h->ev[2], h->stream));
     CU(cudaMemcpyAsync(h->h_ctrl, g.ctrl, sizeof(DenseCtrl), cudaMemcpyDeviceToHost, h->stream));
     f.running = true;

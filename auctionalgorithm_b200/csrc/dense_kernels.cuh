@@ -112,11 +112,14 @@ __device__ __forceinline__ Top2<T> scan_segment_exact(const T* __restrict__ row,
 // One batch = U 128-bit pieces per lane, piece u at column first + u * stride (a warp scanning a
 // row segment: stride 128, first = base + 4 lane; a whole CTA scanning: stride 4 * threads).
 // ---------------------------------------------------------------------------------------------
-template <bool kDeep> struct FilterScan
+// kTrack: also keep max |a| of everything scanned (the fused sharded solve takes the matrix's amax from its first
+// sweep instead of a pass of its own: every row bids in round 1, and with all prices still zero the filter is exact)
+template <bool kDeep, bool kTrack = false> struct FilterScan
 {
     Top2<float> t;
     float thr;
-    __device__ __forceinline__ explicit FilterScan(float thr0) : t(top2_empty<float, kDeep>()), thr(thr0) {}
+    float amax;
+    __device__ __forceinline__ explicit FilterScan(float thr0) : t(top2_empty<float, kDeep>()), thr(thr0), amax(0.f) {}
 };
 
 constexpr int kScanU = 4; // 16-byte loads in flight per lane; 8 is slower (read_probe.cu shows the same for plain reads)
@@ -148,8 +151,8 @@ __device__ __forceinline__ void scan_load(float4 (&a)[kScanU], const float* __re
     }
 }
 
-template <bool kDeep>
-__device__ __forceinline__ void scan_consume(FilterScan<kDeep>& st, const float4 (&a)[kScanU], const double* prices,
+template <bool kDeep, bool kTrack>
+__device__ __forceinline__ void scan_consume(FilterScan<kDeep, kTrack>& st, const float4 (&a)[kScanU], const double* prices,
                                              const float* pricesf, float margin, int first, int stride, int c1)
 {
     constexpr int U = kScanU;
@@ -162,6 +165,8 @@ __device__ __forceinline__ void scan_consume(FilterScan<kDeep>& st, const float4
         {
             const float4 q = *reinterpret_cast<const float4*>(pricesf + cc);
             m = fmaxf(m, fmaxf(fmaxf(a[u].x - q.x, a[u].y - q.y), fmaxf(a[u].z - q.z, a[u].w - q.w)));
+            if (kTrack) // NaNs are ignored, as they are by every comparison of the reference's scan
+                st.amax = fmaxf(st.amax, fmaxf(fmaxf(fabsf(a[u].x), fabsf(a[u].y)), fmaxf(fabsf(a[u].z), fabsf(a[u].w))));
         }
     }
     if (!__any_sync(kFullMask, m > st.thr))
@@ -216,8 +221,8 @@ __device__ __forceinline__ void scan_consume(FilterScan<kDeep>& st, const float4
     }
 }
 
-template <bool kDeep>
-__device__ __forceinline__ void scan_batch(FilterScan<kDeep>& st, const float* __restrict__ row,
+template <bool kDeep, bool kTrack>
+__device__ __forceinline__ void scan_batch(FilterScan<kDeep, kTrack>& st, const float* __restrict__ row,
                                            const double* prices, const float* pricesf, float margin, int first,
                                            int stride, int c1)
 {
@@ -259,6 +264,17 @@ __device__ __forceinline__ Top2<T> scan_segment(const DenseState<T>& s, const T*
     }
     else
         return scan_segment_exact<T, kDeep>(row, s.prices, c0, c1, lane);
+}
+
+// The same, also returning max |a| over the lane's elements (fp32 rows only; see FilterScan).
+__device__ __forceinline__ Top2<float> scan_segment_amax(const DenseState<float>& s, const float* __restrict__ row,
+                                                         float margin, float thr0, int c0, int c1, int lane, float& amax)
+{
+    FilterScan<false, true> st(thr0);
+    for (int base = c0; base < c1; base += 128 * kScanU)
+        scan_batch(st, row, s.prices, s.pricesf, margin, base + lane * 4, 128, c1);
+    amax = fmaxf(amax, st.amax);
+    return st.t;
 }
 
 // Per-thread scan of columns [c0, c1) of a row by a whole CTA: thread t takes the 128-bit pieces
@@ -1010,6 +1026,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     double eps = ctrl->eps[phase < 0 ? 0 : phase]; // phase == -1: k_narrow restarted the schedule (escalate_schedule)
     const double amax = ctrl->amax;
     long long phase_rounds = 0; // wide rounds of the current phase in this launch
+    int small_rounds = 0;       // of those, rounds that could have been narrow (see narrow_after)
     const bool cached = s.use_cache != 0;
     const int narrow_rows = cached ? min(s.narrow_rows, kNarrowMax) : min(min(s.narrow_rows, (int)gridDim.x - 1), kNarrowMax);
     bool handed_over = false;
@@ -1025,6 +1042,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
             phase++;
             eps = ctrl->eps[phase];
             phase_rounds = 0;
+            small_rounds = 0;
             grid.sync(); // everybody has read count[cur] == 0 before it is overwritten
             reset_phase(s, s.list[cur], tid, n_threads);
             if (tid == 0)
@@ -1042,7 +1060,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
                 ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS
             break;
         }
-        if (n <= narrow_rows || n <= min(s.tail_rows, kNarrowMax))
+        bool go_narrow = n <= narrow_rows || n <= min(s.tail_rows, kNarrowMax);
+        if (go_narrow && cached && small_rounds < s.narrow_after)
+        {
+            go_narrow = false; // not yet worth a cache-building sweep of the whole matrix (DenseState::narrow_after)
+            small_rounds++;
+        }
+        if (go_narrow)
         {
             // narrow rounds / Gauss-Seidel tail: finishes the phase without a grid sync per round
             mode_count++;

@@ -247,14 +247,20 @@ __device__ __forceinline__ unsigned long long global_ns()
 // Raise this rank's flag in every mailbox (CTA 0, after a grid sync that follows every writer's system fence),
 // then wait in every CTA until all sources have raised theirs in the local mailbox.  Returns false in a CTA that
 // gave up (it has raised the status; the caller's next grid sync makes that visible to every CTA).
-__device__ __forceinline__ bool shard_exchange(const ShardComm& cm, unsigned long long value, int* status)
+// amax != nullptr: the flag also carries this rank's max |a| (dropped into every mailbox just before the flag).
+__device__ __forceinline__ bool shard_exchange(const ShardComm& cm, unsigned long long value, int* status,
+                                               const volatile double* amax = nullptr)
 {
     __shared__ int timed_out;
     if (threadIdx.x == 0)
         timed_out = 0;
     __syncthreads();
     if (blockIdx.x == 0 && threadIdx.x < cm.n_ranks)
-        st_release_sys(shard_flag(cm, threadIdx.x, cm.rank), value);
+    {
+        if (amax)
+            *reinterpret_cast<volatile double*>(cm.box[threadIdx.x] + 2048 + 8 * cm.rank) = *amax;
+        st_release_sys(shard_flag(cm, threadIdx.x, cm.rank), value); // release: the amax above is visible with it
+    }
     if (threadIdx.x < cm.n_ranks)
     {
         const unsigned long long* f = shard_flag(cm, cm.rank, threadIdx.x);
@@ -293,18 +299,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
     const unsigned long long epoch = *epoch_p;
     unsigned long long x = 0; // exchanges of this solve so far
 
-    // max |a| over all shards (slack of the single-precision filter): every rank drops its own into every mailbox
-    if (tid < cm.n_ranks)
-        *reinterpret_cast<volatile double*>(cm.box[tid] + 2048 + 8 * cm.rank) = ctrl->amax;
-    __threadfence_system();
-    grid.sync();
-    shard_exchange(cm, epoch + ++x, &g.ctrl->status);
-    grid.sync();
-    bool alive = ctrl->status == 0; // uniform: read between two grid syncs
+    // max |a| over all shards (slack of the single-precision filter) is taken from the first sweep: every row bids
+    // in round 1 and, all prices still being zero, a - (float)p is exact there, so that sweep needs no slack itself.
+    // Every rank sends its own maximum along with the flag of round 1.
     double amax = 0.0;
-    for (int q = 0; q < cm.n_ranks; q++)
-        amax = fmax(amax, __ldcg(reinterpret_cast<const double*>(cm.box[cm.rank] + 2048 + 8 * q)));
-
+    bool alive = ctrl->status == 0;
     int cur = 0, phase = 0;
     const int n_phases = ctrl->n_phases;
     const long long max_rounds = ctrl->max_rounds;
@@ -335,6 +334,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
         if (tid == 0)
             ctrl->count[cur ^ 1] = 0;
         const int buf = (int)(x & 1);
+        const bool first_sweep = phase == 0 && rounds == 0; // all prices zero, every row bids
+        float amax_seen = 0.f;
         // ---- bid phase over this rank's columns: bid_phase's scan, the record goes to every mailbox -------------
         {
             const double pmax = fmax(ctrl->pmax, amax);
@@ -349,7 +350,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                 const int b = (int)(item / S), sg = (int)(item - (long long)b * S);
                 const int i = list[b];
                 const int c0 = sg * seg, c1 = min(c0 + seg, l.cols4);
-                Top2<T> t = scan_segment<T>(l, l.A + (long long)i * l.ld, margin, -INFINITY, c0, c1, lane);
+                Top2<T> t;
+                if (first_sweep)
+                    t = scan_segment_amax(l, l.A + (long long)i * l.ld, margin, -INFINITY, c0, c1, lane, amax_seen);
+                else
+                {
+                    // the columns that were best at the row's earlier scans bound its second best from below (dense
+                    // path: cand_threshold): only the batches that hold the row's best columns take the exact path
+                    const float thr0 = S == 1 ? cand_threshold(l, i, margin, lane) : -INFINITY;
+                    t = scan_segment<T>(l, l.A + (long long)i * l.ld, margin, thr0, c0, c1, lane);
+                }
+                if (S == 1 && t.j >= 0)
+                    cand_store(l, i, (t.j >> 2) & (kCand - 1), t.j, t.a);
                 top2_warp_reduce_sparse(t);
                 bool final_warp = S == 1;
                 if (S > 1)
@@ -384,13 +396,31 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                     r.j = t.j >= 0 ? t.j + col0 : -1;
                     r.row = i;
                     shard_slot(cm, lane, buf, cm.rank)[i] = r; // lane q writes rank q's mailbox
+                    __threadfence_system();                    // ... and only the writers pay for a system fence
                 }
             }
+            if (first_sweep)
+            {
+                // non-negative floats order like their bits; the controller keeps the maximum as a double
+#pragma unroll
+                for (int sft = 16; sft >= 1; sft >>= 1)
+                    amax_seen = fmaxf(amax_seen, __shfl_xor_sync(kFullMask, amax_seen, sft));
+                if (lane == 0 && amax_seen > 0.f)
+                    atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->amax),
+                              (unsigned long long)__double_as_longlong((double)amax_seen));
+            }
         }
-        __threadfence_system();
         grid.sync();
         // ---- every rank, identically: merge the ranks' records per bidder, place the bid on the replica ---------
-        if (shard_exchange(cm, epoch + ++x, &g.ctrl->status))
+        const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status, first_sweep ? &ctrl->amax : nullptr);
+        if (first_sweep)
+        {
+            for (int q = 0; q < cm.n_ranks; q++)
+                amax = fmax(amax, __ldcg(reinterpret_cast<const double*>(cm.box[cm.rank] + 2048 + 8 * q)));
+            if (tid == 0)
+                ctrl->amax = amax; // what shard_finish-style readers of the controller block see
+        }
+        if (ok_x)
         {
             const double pmax = fmax(ctrl->pmax, amax);
             const ShardRec* mine = shard_slot(cm, cm.rank, buf, 0);

@@ -170,4 +170,4 @@ def test_c4_full_size_against_reference_golden(handle, oracle_lib):
     got = r2c.cpu().numpy().astype(np.int64)
     verdict = parity.check_parity(a, got, prices.cpu().numpy(), parity.golden_row_to_col(g), 1e-5 / n)
     assert parity.objective(a, got) == pytest.approx(float(g["objective"]), abs=n * 1e-5 / n)
-    print("C4 parity:", verdict)
+    assert verdict == "exact"

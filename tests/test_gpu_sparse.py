@@ -103,6 +103,25 @@ def test_csr_errors_instead_of_hanging(handle):
     with pytest.raises(ab.B200LsapError) as e:
         handle.solve_csr(values, np.array([0, 1, 2, 3], np.int32), np.array([0, 0, 1], np.int32), 3, 3, max_rounds=2000)
     assert e.value.status == ab.ERR_MAX_ROUNDS
+    # column indices outside [0, cols) or not ascending inside a row would index device arrays out of bounds
+    for bad in ([0, 3, 2], [0, -1, 2]):
+        with pytest.raises(ab.B200LsapError) as e:
+            handle.solve_csr(values, np.array([0, 1, 2, 3], np.int32), np.array(bad, np.int32), 3, 3)
+        assert e.value.status == ab.ERR_ARG
+    with pytest.raises(ab.B200LsapError) as e:
+        handle.solve_csr(np.array([0.5, 0.25, 0.75, 0.1]), np.array([0, 2, 3, 4], np.int32), np.array([1, 0, 1, 2], np.int32), 3, 3)
+    assert e.value.status == ab.ERR_ARG
+    # the same checks on device-resident arrays (a validation kernel runs before anything is indexed)
+    import torch
+    out = torch.zeros(3, dtype=torch.int32, device="cuda")
+    v = torch.tensor([0.5, 0.25, 0.75], dtype=torch.float64, device="cuda")
+    for ptr, col, status in (([0, 1, 2, 3], [0, 7, 2], ab.ERR_ARG), ([0, 2, 2, 3], [0, 1, 2], ab.ERR_INFEASIBLE),
+                             ([0, 2, 1, 3], [0, 1, 2], ab.ERR_ARG), ([1, 1, 2, 3], [0, 1, 2], ab.ERR_ARG)):
+        p = torch.tensor(ptr, dtype=torch.int32, device="cuda")
+        c = torch.tensor(col, dtype=torch.int32, device="cuda")
+        with pytest.raises(ab.B200LsapError) as e:
+            handle.solve_csr_device(v.data_ptr(), p.data_ptr(), c.data_ptr(), 3, 3, 3, out.data_ptr(), dtype=np.float64)
+        assert e.value.status == status
     # the handle is still good
     r2c = handle.solve_csr(values, np.array([0, 1, 2, 3], np.int32), np.array([0, 1, 2], np.int32), 3, 3)
     assert list(r2c) == [0, 1, 2]

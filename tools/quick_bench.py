@@ -70,6 +70,40 @@ if __name__ == "__main__":
                 dbg = h.debug_counters()
                 if any(dbg[:4]):
                     print("   takeover cycles [eval, shfl, update, next-row]:", dbg[:4], flush=True)
+    if "c5" in which:   # 65536 x 98304 on one GPU: the dense solver, its wide rounds alone, the fused sharded kernel, one sweep
+        from auctionalgorithm_b200 import sharded
+        rows, cols = 65536, 98304
+        t = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+        h.generate_shard_device(t.data_ptr(), rows, cols, cols, 0, cols, 1)
+        r2c = torch.empty(rows, dtype=torch.int32, device="cuda")
+        for opt in (dict(), dict(tail_rows=-1, narrow_rows=-1)):
+            for _ in range(2):
+                st = h.solve_device(t.data_ptr(), rows, cols, cols, 1, r2c.data_ptr(), **opt)
+            print(f"c5 dense {opt}: {st['ms_solve']:.3f} ms rounds {st['rounds']} bids {st['bids']} narrow {st['narrow_rounds']} launches {st['launches']}", flush=True)
+        for _ in range(3):
+            ms, nb = h.bid_sweep_device(t.data_ptr(), rows, cols, cols, False)
+        print(f"c5 first sweep: {ms:.3f} ms -> {nb/ms/1e6:.0f} GB/s", flush=True)
+        h.shard_comm_create(rows, 1); h.shard_comm_connect(0, 1)
+        for _ in range(2):
+            r, p, st = sharded.solve_fused(h, t, rows, cols, cols, 0, cols)
+        print(f"c5 fused N=1: {st['ms_solve']:.3f} ms rounds {st['rounds']} bids {st['bids']}", flush=True)
+        dbg = h.debug_counters()
+        if any(dbg):
+            print("   dbg:", dbg, flush=True)
+    if "c5n" in which:   # bidders per round of C5 (host-driven form, one shard) with the kernels' times
+        rows, cols = 65536, 98304
+        t = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+        h.generate_shard_device(t.data_ptr(), rows, cols, cols, 0, cols, 1)
+        amax = h.shard_begin(t.data_ptr(), rows, cols, cols, 0, cols)
+        h.shard_set_amax(amax)
+        send = torch.empty(rows * 32, dtype=torch.uint8, device="cuda")
+        n, out = rows, []
+        while n > 0:
+            torch.cuda.synchronize(); t0 = time.perf_counter()
+            h.shard_bid(send.data_ptr()); torch.cuda.synchronize(); t1 = time.perf_counter()
+            n2 = h.shard_resolve(send.data_ptr(), 1); t2 = time.perf_counter()
+            out.append((n, (t1 - t0) * 1e6, (t2 - t1) * 1e6)); n = n2
+        print("c5 rounds (bidders, bid us, resolve us):", [(a, round(b), round(c)) for a, b, c in out], flush=True)
     if "monster1" in which:  # one launch of the slowest problem alone (ncu source-level profile of the takeover)
         t = torch.empty((1, 32, 48), dtype=torch.float32, device="cuda")
         out = torch.empty((1, 32), dtype=torch.int32, device="cuda")

@@ -8,7 +8,7 @@ from oracle import pyoracle as po
 import parity
 
 h = ab.Handle(0)
-which = sys.argv[1:] or ["dense", "pairs", "sparse", "batch"]
+which = sys.argv[1:] or ["dense", "pairs", "sparse", "batch", "fused"]
 if "dense" in which:
     for rows, cols in ((200, 300), (256, 256), (700, 700)):
         a = po.generate(rows, cols, 1)
@@ -29,7 +29,33 @@ if "sparse" in which:
         assert parity.is_valid_assignment(r, cols)
         print("sparse", rows, cols, len(v), h.last_stats["rounds"], flush=True)
 if "batch" in which:
-    a = np.stack([po.generate(32, 48, 1, problem=b) for b in range(64)])
-    r = h.solve_batch(a)
-    print("batch", r.shape, flush=True)
+    # two-lane pass, dynamic hand-out over more than one reservation, takeover by cap (forced at 8 bids) and by a
+    # real price war (problem 1117884 of the bench shards: 1483 bids), half last chunks (cols % 8 == 4)
+    a = np.stack([po.generate(32, 48, 1, problem=b) for b in [1117884] + list(range(200))])
+    ref, failed = po.oracle_batch(a, use_double=True, n_threads=4)
+    assert failed == 0
+    for cap in (0, 8, -1):
+        assert np.array_equal(h.solve_batch(a, batch_bid_cap=cap), ref)
+    b = np.stack([po.generate(20, 44, 2, problem=k) for k in range(100)])
+    ref, _ = po.oracle_batch(b, use_double=True, n_threads=4)
+    assert np.array_equal(h.solve_batch(b, batch_bid_cap=4), ref)
+    c = np.stack([po.generate(9, 13, 3, problem=k) for k in range(50)])     # streaming kernel (cols % 4 != 0)
+    ref, _ = po.oracle_batch(c, use_double=True, n_threads=4)
+    assert np.array_equal(h.solve_batch(c), ref)
+    print("batch", a.shape, b.shape, c.shape, flush=True)
+if "fused" in which:
+    # column-sharded solve, three ranks on this GPU: peer stores into the mailboxes, release / acquire flags
+    import torch
+    from auctionalgorithm_b200 import sharded
+    hs = [ab.Handle(0) for _ in range(3)]
+    sharded.connect_fused_local(hs, 256)
+    for rows, cols in ((200, 300), (256, 256)):
+        a = po.generate(rows, cols, 1)
+        parts = sharded.split_columns(cols, 3)
+        shards = [torch.from_numpy(np.ascontiguousarray(a[:, c0:c0 + cl])).cuda() for c0, cl in parts]
+        res = sharded.solve_fused_local(hs, shards, rows, parts, [cl for _, cl in parts], cols)
+        assert parity.is_valid_assignment(res[0][0].cpu().numpy(), cols)
+        print("fused", rows, cols, res[0][2]["rounds"], flush=True)
+    for x in hs:
+        x.close()
 print("done")

@@ -1702,7 +1702,10 @@ int b200lsap_solve_sharded_begin_f32(b200lsap_handle* h, const float* a_dev, int
     k_init<float><<<grid, kThreads, 0, h->stream>>>(g, 0);
     // (no pass over the matrix for max |a|: the kernel takes it from its first sweep)
     int c0 = (int)col0;
-    void* args[] = {(void*)&l, (void*)&g, (void*)&f.cm, (void*)&c0};
+    // rounds whose rows amount to at most this many bytes per rank are played by one CTA (B200LSAP_SHARD_SMALL_KB)
+    static const long long small_env = getenv("B200LSAP_SHARD_SMALL_KB") ? atoll(getenv("B200LSAP_SHARD_SMALL_KB")) : -1;
+    long long small_bytes = small_env >= 0 ? small_env * 1024 : 1024 * 1024;
+    void* args[] = {(void*)&l, (void*)&g, (void*)&f.cm, (void*)&c0, (void*)&small_bytes};
     CU(cudaLaunchCooperativeKernel((void*)k_shard_persistent<float>, dim3(grid), dim3(kThreads), args, 0, h->stream));
     h->launches += 2;
     CU(cudaEventRecord(h->ev[2], h->stream));

@@ -90,6 +90,7 @@ struct DenseCtrl
     double pmax;            // upper bound of every price so far (monotone; bits ordered as u64)
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)
     double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
+    unsigned long long shard_x; // fused sharded solve: exchanges so far (handed from CTA 0 back to the grid)
 };
 
 // Slack of the single-precision filter of scan_segment_filtered: with |a| <= amax, 0 <= p <= pbound,

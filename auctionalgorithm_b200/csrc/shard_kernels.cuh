@@ -281,12 +281,169 @@ __device__ __forceinline__ bool shard_exchange(const ShardComm& cm, unsigned lon
     return timed_out == 0;
 }
 
+// How many segments a bidder's row is cut into.  split_factor (dense path) takes the largest power of two that keeps
+// n * S <= warps, which leaves up to half of the machine idle (2992 bidders on 4736 warps: S = 1, 63 % busy, and the
+// round lasts as long as one warp needs for a whole 393 KB row) and rounds the number of waves up when there are more
+// bidders than warps (7781 bidders: 2 waves for 1.64 waves of work).  Here S is any integer and the items may take
+// several waves: the S that minimises waves(n * S) * (row time / S + item overhead), with a warp streaming
+// ~1.7 GB/s (four 512-byte pieces in flight per ~1.2 us of latency) and ~3 us per item for the partial result, the
+// fence and the ticket.
+// (Measured on 65536 x 98304, one GPU: 10.9 ms with this rule against 9.4-9.8 ms with split_factor's powers of two:
+// the split-row path costs more per item than the model assumes.  Kept for experiments, off by default.)
+#ifndef B200LSAP_SHARD_SPLIT_MODEL
+#define B200LSAP_SHARD_SPLIT_MODEL 0
+#endif
+constexpr bool kShardSplitModel = B200LSAP_SHARD_SPLIT_MODEL != 0;
+__device__ __forceinline__ int shard_split(int n, int n_warps, int cols4, int min_seg, long long cap_items)
+{
+    int s_max = min(128, max(1, cols4 / max(min_seg, 128)));
+    s_max = (int)min((long long)s_max, max(1ll, cap_items / n));
+    const float t_row = (float)cols4 * (4.0f / 1700.0f), t_item = 3.0f; // microseconds
+    int best = 1;
+    float best_cost = (float)((n + n_warps - 1) / n_warps) * t_row;
+    for (int s = 2; s <= s_max; s++)
+    {
+        const long long items = (long long)n * s;
+        const float cost = (float)((items + n_warps - 1) / n_warps) * (t_row / (float)s + t_item);
+        if (cost < 0.97f * best_cost)
+        {
+            best = s;
+            best_cost = cost;
+        }
+    }
+    return best;
+}
+
+// Bid phase of a round over this rank's columns (bid_phase's scan): n_warps warps, numbered warp_id, share the n
+// bidders of `list` (whole rows, or S segments per row merged by the last warp to arrive); the warp that completes a
+// row stores its record into every rank's mailbox.  first_sweep: all prices are zero (round 1 of the solve), the
+// scan also collects max |a| (amax_seen, per lane).
+template <typename T>
+__device__ __forceinline__ void shard_bid_phase(const DenseState<T>& l, const ShardComm& cm, int col0,
+                                                const int* __restrict__ list, int n, int buf, bool first_sweep,
+                                                float margin, int warp_id, int n_warps, int lane, float& amax_seen,
+                                                long long cap_items)
+{
+    const int S = kShardSplitModel ? shard_split(n, n_warps, l.cols4, l.min_seg, cap_items)
+                                   : split_factor(n, n_warps, l.cols4, l.min_seg);
+    int seg = (l.cols4 + S - 1) / S;
+    seg = (seg + 127) & ~127;
+    const long long items = (long long)n * S;
+    for (long long item = warp_id; item < items; item += n_warps)
+    {
+        const int b = (int)(item / S), sg = (int)(item - (long long)b * S);
+        const int i = list[b];
+        const int c0 = sg * seg, c1 = min(c0 + seg, l.cols4);
+        Top2<T> t;
+        if (first_sweep)
+            t = scan_segment_amax(l, l.A + (long long)i * l.ld, margin, -INFINITY, c0, c1, lane, amax_seen);
+        else
+        {
+            // the columns that were best at the row's earlier scans bound its second best from below (dense
+            // path: cand_threshold): only the batches that hold the row's best columns take the exact path
+            // (a property of the ROW: it holds for every segment; candidates are any true edges of the row, so
+            // segments may store theirs concurrently: 8-byte stores, whichever lands is an edge)
+            const float thr0 = cand_threshold(l, i, margin, lane);
+            t = scan_segment<T>(l, l.A + (long long)i * l.ld, margin, thr0, c0, c1, lane);
+        }
+        if (t.j >= 0)
+            cand_store(l, i, (t.j >> 2) & (kCand - 1), t.j, t.a);
+        top2_warp_reduce_sparse(t);
+        bool final_warp = S == 1;
+        if (S > 1)
+        {
+            int ticket = 0;
+            if (lane == 0)
+            {
+                l.partial[(long long)b * S + sg] = t;
+                __threadfence();
+                ticket = atomicAdd(&l.arrive[b], 1);
+            }
+            ticket = __shfl_sync(kFullMask, ticket, 0);
+            if (ticket == S - 1)
+            {
+                __threadfence();
+                Top2<T> m = top2_empty<T>();
+                for (int k = lane; k < S; k += 32)
+                    top2_merge(m, top2_load_cg(&l.partial[(long long)b * S + k]));
+                top2_warp_reduce(m);
+                t = m;
+                final_warp = true;
+                if (lane == 0)
+                    l.arrive[b] = 0;
+            }
+        }
+        if (final_warp && lane < cm.n_ranks)
+        {
+            ShardRec r;
+            r.v = t.v;
+            r.w = t.w;
+            r.a = (double)t.a;
+            r.j = t.j >= 0 ? t.j + col0 : -1;
+            r.row = i;
+            shard_slot(cm, lane, buf, cm.rank)[i] = r; // lane q writes rank q's mailbox
+            __threadfence_system();                    // ... and only the writers pay for a system fence
+        }
+    }
+}
+
+// Every rank, identically: merge the ranks' records of each bidder (rank order = column order, so top2_merge's
+// "lowest column wins ties" is AuctionMT's interval order, AuctionMT.h:377-398) and place the bid on the replica.
+template <typename T>
+__device__ __forceinline__ void shard_merge_phase(const DenseState<T>& g, const ShardComm& cm, const int* __restrict__ list,
+                                                  int n, int buf, double eps, double pmax, long long tid, long long n_threads)
+{
+    const ShardRec* mine = shard_slot(cm, cm.rank, buf, 0);
+    for (long long b = tid; b < n; b += n_threads)
+    {
+        const int i = list[b];
+        Top2<double> m;
+        m.v = m.w = -kNoSecondBest;
+        m.j = -1;
+        m.a = 0.0;
+        bool ok = true;
+        for (int r = 0; r < cm.n_ranks; r++)
+        {
+            // (written by a peer during this kernel: L2 loads, never the non-coherent path)
+            const double2* rp = reinterpret_cast<const double2*>(mine + r * cm.rows_cap + i);
+            const double2 lo = __ldcg(rp), hi = __ldcg(rp + 1);
+            Top2<double> o;
+            o.v = lo.x;
+            o.w = lo.y;
+            o.a = hi.x;
+            o.j = (int)(__double_as_longlong(hi.y) & 0xffffffffll);
+            ok = ok && (int)(__double_as_longlong(hi.y) >> 32) == i;
+            top2_merge(m, o);
+        }
+        if (!ok || m.j < 0)
+        {
+            g.ctrl->status = ok ? 2 : 4; // infeasible row / a record that is not this row's
+            g.bid_col[i] = -1;
+            continue;
+        }
+        const double bid = m.a - m.w + eps; // Auction.h:250
+        g.bid_col[i] = m.j;
+        g.bid_val[i] = bid;
+        g.profits[i] = m.w - eps; // Auction.h:253
+        slot_offer(&g.slots[m.j], bid, i);
+        if (bid > pmax)
+            atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->pmax), (unsigned long long)__double_as_longlong(bid));
+    }
+}
+
 // l: the scan view (this rank's columns; prices / pricesf offset to its first column), g: the global view (all
 // columns; the replicated state).  Both share the controller block and the lists.
+//
+// Small rounds.  Most ROUNDS of a solve have a handful of bidders (65536 x 98304: 45 of the 64 rounds have at most
+// 64) and cost three grid syncs each, ~45 us, for microseconds of work.  Bidders never increase inside an eps phase,
+// so once a round's rows fit one CTA's reach (n * local columns * 4 bytes <= small_bytes) CTA 0 plays the rest of the
+// phase alone — same phases, block barriers instead of grid syncs, the same exchange — while the other CTAs wait at
+// one grid sync.  Every rank takes the decision from the replicated bidder count, so all switch in the same round.
 template <typename T>
 __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_constant__ DenseState<T> l,
                                                                    const __grid_constant__ DenseState<T> g,
-                                                                   const __grid_constant__ ShardComm cm, int col0)
+                                                                   const __grid_constant__ ShardComm cm, int col0,
+                                                                   long long small_bytes)
 {
     cg::grid_group grid = cg::this_grid();
     const int lane = threadIdx.x & 31;
@@ -298,18 +455,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
     unsigned long long* epoch_p = reinterpret_cast<unsigned long long*>(cm.box[cm.rank] + 3072);
     const unsigned long long epoch = *epoch_p;
     unsigned long long x = 0; // exchanges of this solve so far
+    const long long cap_items = max((long long)total_warps + 64, 4ll * g.rows); // entries of l.partial (alloc_state)
 
     // max |a| over all shards (slack of the single-precision filter) is taken from the first sweep: every row bids
     // in round 1 and, all prices still being zero, a - (float)p is exact there, so that sweep needs no slack itself.
     // Every rank sends its own maximum along with the flag of round 1.
     double amax = 0.0;
-    bool alive = ctrl->status == 0;
     int cur = 0, phase = 0;
     const int n_phases = ctrl->n_phases;
     const long long max_rounds = ctrl->max_rounds;
     long long rounds = 0, bids = 0;
     double eps = ctrl->eps[0];
-    while (alive)
+    while (ctrl->status == 0)
     {
         const int n = ctrl->count[cur];
         if (n == 0)
@@ -331,138 +488,87 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                 ctrl->status = 3; // B200LSAP_ERR_MAX_ROUNDS (replicated state: every rank stops here)
             break;
         }
+        const bool first_sweep = phase == 0 && rounds == 0; // all prices zero, every row bids
+        if (!first_sweep && n <= kThreads && (long long)n * l.cols4 * (long long)sizeof(T) <= small_bytes)
+        {
+            // ---- the rest of this phase on CTA 0 ------------------------------------------------------------------
+            if (blockIdx.x == 0)
+            {
+                int m = n;
+                while (m > 0 && rounds < max_rounds)
+                {
+                    if (threadIdx.x == 0)
+                        ctrl->count[cur ^ 1] = 0;
+                    const int buf = (int)(x & 1);
+                    const double pmax = fmax(ctrl->pmax, amax);
+                    float unused = 0.f;
+                    shard_bid_phase<T>(l, cm, col0, g.list[cur], m, buf, false, filter_margin(amax, pmax), threadIdx.x >> 5,
+                                       kWarpsPerBlock, lane, unused, cap_items);
+                    __syncthreads();
+                    const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status);
+                    if (ok_x)
+                        shard_merge_phase<T>(g, cm, g.list[cur], m, buf, eps, pmax, threadIdx.x, kThreads);
+                    __threadfence(); // bids, slots: performed before anybody of this CTA reads them back
+                    __syncthreads();
+                    if (ctrl->status != 0)
+                        break;
+                    resolve_phase<T>(g, g.list[cur], m, g.list[cur ^ 1], &g.ctrl->count[cur ^ 1], threadIdx.x, kThreads, lane);
+                    __threadfence();
+                    __syncthreads();
+                    cur ^= 1;
+                    rounds++;
+                    bids += m;
+                    m = ctrl->count[cur];
+                }
+                if (threadIdx.x == 0)
+                {
+                    if (m > 0 && ctrl->status == 0)
+                        ctrl->status = 3; // the round watchdog
+                    ctrl->cur = cur;
+                    ctrl->rounds = rounds;
+                    ctrl->bids = bids;
+                    ctrl->shard_x = x;
+                }
+            }
+            grid.sync();
+            cur = ctrl->cur;
+            rounds = ctrl->rounds;
+            bids = ctrl->bids;
+            x = ctrl->shard_x;
+            grid.sync(); // everybody has the state before CTA 0 moves on (it may overwrite count / cur next)
+            continue;
+        }
         if (tid == 0)
             ctrl->count[cur ^ 1] = 0;
         const int buf = (int)(x & 1);
-        const bool first_sweep = phase == 0 && rounds == 0; // all prices zero, every row bids
         float amax_seen = 0.f;
-        // ---- bid phase over this rank's columns: bid_phase's scan, the record goes to every mailbox -------------
+        const double pmax = fmax(ctrl->pmax, amax);
+        shard_bid_phase<T>(l, cm, col0, g.list[cur], n, buf, first_sweep, filter_margin(amax, pmax), warp_global, total_warps,
+                           lane, amax_seen, cap_items);
+        if (first_sweep)
         {
-            const double pmax = fmax(ctrl->pmax, amax);
-            const float margin = filter_margin(amax, pmax);
-            const int* __restrict__ list = g.list[cur];
-            const int S = split_factor(n, total_warps, l.cols4, l.min_seg);
-            int seg = (l.cols4 + S - 1) / S;
-            seg = (seg + 127) & ~127;
-            const long long items = (long long)n * S;
-            for (long long item = warp_global; item < items; item += total_warps)
-            {
-                const int b = (int)(item / S), sg = (int)(item - (long long)b * S);
-                const int i = list[b];
-                const int c0 = sg * seg, c1 = min(c0 + seg, l.cols4);
-                Top2<T> t;
-                if (first_sweep)
-                    t = scan_segment_amax(l, l.A + (long long)i * l.ld, margin, -INFINITY, c0, c1, lane, amax_seen);
-                else
-                {
-                    // the columns that were best at the row's earlier scans bound its second best from below (dense
-                    // path: cand_threshold): only the batches that hold the row's best columns take the exact path
-                    const float thr0 = S == 1 ? cand_threshold(l, i, margin, lane) : -INFINITY;
-                    t = scan_segment<T>(l, l.A + (long long)i * l.ld, margin, thr0, c0, c1, lane);
-                }
-                if (S == 1 && t.j >= 0)
-                    cand_store(l, i, (t.j >> 2) & (kCand - 1), t.j, t.a);
-                top2_warp_reduce_sparse(t);
-                bool final_warp = S == 1;
-                if (S > 1)
-                {
-                    int ticket = 0;
-                    if (lane == 0)
-                    {
-                        l.partial[(long long)b * S + sg] = t;
-                        __threadfence();
-                        ticket = atomicAdd(&l.arrive[b], 1);
-                    }
-                    ticket = __shfl_sync(kFullMask, ticket, 0);
-                    if (ticket == S - 1)
-                    {
-                        __threadfence();
-                        Top2<T> m = top2_empty<T>();
-                        for (int k = lane; k < S; k += 32)
-                            top2_merge(m, top2_load_cg(&l.partial[(long long)b * S + k]));
-                        top2_warp_reduce(m);
-                        t = m;
-                        final_warp = true;
-                        if (lane == 0)
-                            l.arrive[b] = 0;
-                    }
-                }
-                if (final_warp && lane < cm.n_ranks)
-                {
-                    ShardRec r;
-                    r.v = t.v;
-                    r.w = t.w;
-                    r.a = (double)t.a;
-                    r.j = t.j >= 0 ? t.j + col0 : -1;
-                    r.row = i;
-                    shard_slot(cm, lane, buf, cm.rank)[i] = r; // lane q writes rank q's mailbox
-                    __threadfence_system();                    // ... and only the writers pay for a system fence
-                }
-            }
-            if (first_sweep)
-            {
-                // non-negative floats order like their bits; the controller keeps the maximum as a double
+            // non-negative floats order like their bits; the controller keeps the maximum as a double
 #pragma unroll
-                for (int sft = 16; sft >= 1; sft >>= 1)
-                    amax_seen = fmaxf(amax_seen, __shfl_xor_sync(kFullMask, amax_seen, sft));
-                if (lane == 0 && amax_seen > 0.f)
-                    atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->amax),
-                              (unsigned long long)__double_as_longlong((double)amax_seen));
-            }
+            for (int sft = 16; sft >= 1; sft >>= 1)
+                amax_seen = fmaxf(amax_seen, __shfl_xor_sync(kFullMask, amax_seen, sft));
+            if (lane == 0 && amax_seen > 0.f)
+                atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->amax),
+                          (unsigned long long)__double_as_longlong((double)amax_seen));
         }
         grid.sync();
-        // ---- every rank, identically: merge the ranks' records per bidder, place the bid on the replica ---------
         const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status, first_sweep ? &ctrl->amax : nullptr);
         if (first_sweep)
         {
             for (int q = 0; q < cm.n_ranks; q++)
                 amax = fmax(amax, __ldcg(reinterpret_cast<const double*>(cm.box[cm.rank] + 2048 + 8 * q)));
-            if (tid == 0)
-                ctrl->amax = amax; // what shard_finish-style readers of the controller block see
         }
         if (ok_x)
-        {
-            const double pmax = fmax(ctrl->pmax, amax);
-            const ShardRec* mine = shard_slot(cm, cm.rank, buf, 0);
-            for (long long b = tid; b < n; b += n_threads)
-            {
-                const int i = g.list[cur][b];
-                Top2<double> m;
-                m.v = m.w = -kNoSecondBest;
-                m.j = -1;
-                m.a = 0.0;
-                bool ok = true;
-                for (int r = 0; r < cm.n_ranks; r++)
-                {
-                    // (written by a peer during this kernel: L2 loads, never the non-coherent path)
-                    const double2* rp = reinterpret_cast<const double2*>(mine + r * cm.rows_cap + i);
-                    const double2 lo = __ldcg(rp), hi = __ldcg(rp + 1);
-                    Top2<double> o;
-                    o.v = lo.x;
-                    o.w = lo.y;
-                    o.a = hi.x;
-                    o.j = (int)(__double_as_longlong(hi.y) & 0xffffffffll);
-                    ok = ok && (int)(__double_as_longlong(hi.y) >> 32) == i;
-                    top2_merge(m, o);
-                }
-                if (!ok || m.j < 0)
-                {
-                    g.ctrl->status = ok ? 2 : 4; // infeasible row / a record that is not this row's
-                    g.bid_col[i] = -1;
-                    continue;
-                }
-                const double bid = m.a - m.w + eps; // Auction.h:250
-                g.bid_col[i] = m.j;
-                g.bid_val[i] = bid;
-                g.profits[i] = m.w - eps; // Auction.h:253
-                slot_offer(&g.slots[m.j], bid, i);
-                if (bid > pmax)
-                    atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->pmax), (unsigned long long)__double_as_longlong(bid));
-            }
-        }
+            shard_merge_phase<T>(g, cm, g.list[cur], n, buf, eps, pmax, tid, n_threads);
         grid.sync();
         if (ctrl->status != 0)
             break;
+        if (first_sweep && tid == 0)
+            ctrl->amax = amax; // the maximum over all ranks, for readers of the controller block
         resolve_phase<T>(g, g.list[cur], n, g.list[cur ^ 1], &g.ctrl->count[cur ^ 1], tid, n_threads, lane);
         grid.sync();
         cur ^= 1;

@@ -36,7 +36,7 @@ def test_sharded_solve_on_real_ranks_matches_the_reference(tmp_path, name, world
     res = json.load(open(out))
     assert res["fused_exact"], res
     assert res["replicas_identical"] and res["host_driven_equal"], res
-    assert res["eps_cs_violation_local_columns"] <= res["eps"] * (1 + 1e-9), res
+    assert res["eps_cs_violation_local_columns"] <= res["eps"] * (1 + 1e-9) + 1e-15, res   # a few ulps of the fp64 check itself
 
 
 def test_multi_handle_solves_across_devices_in_one_process(oracle_lib):

@@ -79,6 +79,14 @@ SIGNATURES = {
     "b200lsap_solve_sharded_end": (C.c_int, [_H, _P, _P, C.POINTER(Stats)]),
     "b200lsap_solve_sharded_device_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, _i64, _i64, C.POINTER(Options), _P, _P,
                                                     C.POINTER(Stats)]),
+    "b200lsap_create_multi": (C.c_int, [C.POINTER(_H), C.POINTER(C.c_int), C.c_int]),
+    "b200lsap_destroy_multi": (C.c_int, [_H]),
+    "b200lsap_multi_last_error": (C.c_char_p, [_H]),
+    "b200lsap_multi_devices": (C.c_int, [_H]),
+    "b200lsap_multi_solve_f32": (C.c_int, [_H, _P, _i64, _i64, _i64, C.c_int, C.POINTER(Options), _P, _P,
+                                           C.POINTER(Stats)]),
+    "b200lsap_multi_solve_batch_f32": (C.c_int, [_H, _P, _i64, C.c_int32, C.c_int32, C.c_int, C.POINTER(Options), _P,
+                                                 C.POINTER(Stats)]),
     "b200lsap_debug_counters": (C.c_int, [_H, C.POINTER(_i64), C.c_int]),
     "b200lsap_host_alloc": (C.c_void_p, [_i64]),
     "b200lsap_host_free": (None, [_P]),

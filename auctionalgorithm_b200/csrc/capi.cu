@@ -4,6 +4,7 @@
 // themselves run in dense_kernels.cuh / batch_kernels.cuh.  There is no CPU solve path.
 #include "../../include/b200lsap.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -51,6 +52,8 @@ struct DevBuf
 
 } // namespace
 
+constexpr int kBatchSlots = 16; // control blocks of batched launches in flight on one handle (chunked host entry)
+
 struct b200lsap_handle
 {
     int device = 0;
@@ -61,7 +64,9 @@ struct b200lsap_handle
     DevBuf a, staging, csr_ptr, csr_col, csr_val, prices, pricesf, cand, cache, cache_hdr, narrow, profits, slots, owner, row2col, bid_col, bid_val, list0, list1, partial, arrive,
         ctrl, out64, batch_in, batch_out, batch_ctrl;
     DenseCtrl* h_ctrl = nullptr; // pinned mirror
-    BatchCtrl* h_bctrl = nullptr; // pinned mirror of the batched launch's control block
+    BatchCtrl* h_bctrl = nullptr; // pinned mirrors of the batched launches' control blocks (kBatchSlots of them)
+    cudaStream_t up = nullptr, down = nullptr; // host entry of the batched mode: H2D / D2H beside the kernels
+    cudaEvent_t ev_up[16] = {}, ev_done[16] = {};
     std::map<const void*, int> occupancy; // kernel -> resident CTAs per SM (attributes set once per handle)
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int64_t last_cols = 0; // prices of the last dense solve are valid for this many columns
@@ -188,7 +193,9 @@ int b200lsap_create(b200lsap_handle** out, int device)
         cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMallocHost((void**)&h->h_ctrl, sizeof(DenseCtrl)) != cudaSuccess ||
-        cudaMallocHost((void**)&h->h_bctrl, sizeof(BatchCtrl)) != cudaSuccess)
+        cudaMallocHost((void**)&h->h_bctrl, kBatchSlots * sizeof(BatchCtrl)) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->up, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->down, cudaStreamNonBlocking) != cudaSuccess)
     {
         delete h;
         return B200LSAP_ERR_CUDA;
@@ -196,6 +203,11 @@ int b200lsap_create(b200lsap_handle** out, int device)
     h->own_stream = true;
     for (auto& e : h->ev)
         cudaEventCreate(&e);
+    for (int k = 0; k < kBatchSlots; k++)
+    {
+        cudaEventCreateWithFlags(&h->ev_up[k], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&h->ev_done[k], cudaEventDisableTiming);
+    }
     if (const char* s = getenv("B200LSAP_MAX_PARTS"))
     {
         int v = atoi(s);
@@ -240,6 +252,17 @@ int b200lsap_destroy(b200lsap_handle* h)
         cudaFreeHost(h->h_ctrl);
     if (h->h_bctrl)
         cudaFreeHost(h->h_bctrl);
+    for (int k = 0; k < kBatchSlots; k++)
+    {
+        if (h->ev_up[k])
+            cudaEventDestroy(h->ev_up[k]);
+        if (h->ev_done[k])
+            cudaEventDestroy(h->ev_done[k]);
+    }
+    if (h->up)
+        cudaStreamDestroy(h->up);
+    if (h->down)
+        cudaStreamDestroy(h->down);
     if (h->own_stream && h->stream)
         cudaStreamDestroy(h->stream);
     delete h;
@@ -1043,8 +1066,34 @@ int batch_occupancy(b200lsap_handle* h, const void* kernel, int threads, size_t 
     return B200LSAP_OK;
 }
 
+// After the stream has been synchronised: statistics and status of the launches that used slots [slot0, slot0 + n).
+int batch_collect(b200lsap_handle* h, int slot0, int n, b200lsap_stats* stats)
+{
+    int status = 0;
+    for (int k = slot0; k < slot0 + n; k++)
+    {
+        const BatchCtrl& c = h->h_bctrl[k];
+        if (stats)
+        {
+            stats->batch_takeovers += c.takeovers;
+            stats->batch_max_bids = std::max<int64_t>(stats->batch_max_bids, c.max_bids);
+            stats->cache_hits += (int64_t)c.hits;     // takeover bids answered from a row cache
+            stats->cache_misses += (int64_t)c.misses; // ... by a full scan of the row
+        }
+        for (int d = 0; d < 4; d++)
+            h->h_ctrl->dbg[d] = (long long)c.dbg[d]; // b200lsap_debug_counters
+        if (c.status != 0 && status == 0)
+            status = c.status;
+    }
+    if (status != 0)
+        return fail(h, status, b200lsap_status_string(status));
+    return B200LSAP_OK;
+}
+
+// slot: which of the handle's control blocks the launch uses (launches of one call that are in flight together take
+// different slots); sync = false: enqueue only, the caller synchronises and calls batch_collect.
 int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, int rows, int cols,
-              const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats, bool sync = true)
+              const b200lsap_options* opts, int32_t* r2c_dev, b200lsap_stats* stats, bool sync = true, int slot = 0)
 {
     b200lsap_options o;
     b200lsap_options_default(&o);
@@ -1060,8 +1109,8 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     P.cols = cols;
     P.eps = o.eps_multiplier / (double)cols;
     P.max_bids = o.max_rounds > 0 ? (int)(o.max_rounds > 0x7fffffff ? 0x7fffffff : o.max_rounds) : 1000000;
-    CU(h->batch_ctrl.ensure(sizeof(BatchCtrl)));
-    P.ctl = h->batch_ctrl.as<BatchCtrl>();
+    CU(h->batch_ctrl.ensure(kBatchSlots * sizeof(BatchCtrl)));
+    P.ctl = h->batch_ctrl.as<BatchCtrl>() + slot;
     P.status = &P.ctl->status;
     // B200LSAP_BATCH_CAP / B200LSAP_BATCH_CHUNK: developer A/B knobs of the filtered kernel
     static const int cap_env = getenv("B200LSAP_BATCH_CAP") ? atoi(getenv("B200LSAP_BATCH_CAP")) : 0;
@@ -1149,9 +1198,9 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
     }
     h->launches++;
     CU(cudaEventRecord(h->ev[2], h->stream));
-    CU(cudaMemcpyAsync(h->h_bctrl, P.ctl, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(h->h_bctrl + slot, P.ctl, sizeof(BatchCtrl), cudaMemcpyDeviceToHost, h->stream));
     if (!sync)
-        return B200LSAP_OK; // the caller synchronises and calls finish_batch
+        return B200LSAP_OK; // the caller synchronises and calls batch_collect
     CU(cudaStreamSynchronize(h->stream));
     CU(cudaGetLastError());
     if (stats)
@@ -1162,16 +1211,8 @@ int run_batch(b200lsap_handle* h, const float* a_dev_row_major, int64_t batch, i
         stats->eps_final = P.eps;
         stats->bid_bytes = batch * ((int64_t)rows * cols * 4 + rows * 4);
         stats->launches = h->launches;
-        stats->batch_takeovers = h->h_bctrl->takeovers;
-        stats->batch_max_bids = h->h_bctrl->max_bids;
-        stats->cache_hits = (int64_t)h->h_bctrl->hits;     // takeover bids answered from a row cache
-        stats->cache_misses = (int64_t)h->h_bctrl->misses; // ... by a full scan of the row
-        for (int k = 0; k < 4; k++)
-            h->h_ctrl->dbg[k] = (long long)h->h_bctrl->dbg[k]; // b200lsap_debug_counters
     }
-    if (h->h_bctrl->status != 0)
-        return fail(h, h->h_bctrl->status, b200lsap_status_string(h->h_bctrl->status));
-    return B200LSAP_OK;
+    return batch_collect(h, slot, 1, stats);
 }
 
 int check_batch(b200lsap_handle* h, const void* a, int64_t batch, int rows, int cols, int layout, const void* out)
@@ -1216,6 +1257,85 @@ int b200lsap_solve_batch_device_f32(b200lsap_handle* h, const float* a_dev, int6
     return run_batch(h, src, batch, rows, cols, opts, r2c_dev, stats);
 }
 
+} // extern "C"
+
+namespace
+{
+
+// Host arrays in and out.  The batch crosses PCIe in chunks: the upload of chunk k + 1, the kernel on chunk k and the
+// download of chunk k - 1 run on three streams, so the call is bound by the link (6144 bytes per 32x48 problem) and
+// not by copy + solve + copy in a row.  enqueue / wait are split so that b200lsap_multi can drive several devices.
+int batch_host_enqueue(b200lsap_handle* h, const float* a, int64_t batch, int rows, int cols, int layout,
+                       const b200lsap_options* opts, int32_t* row_to_col, int& n_chunks)
+{
+    CU(cudaSetDevice(h->device));
+    h->launches = 0;
+    const int64_t per = (int64_t)rows * cols;
+    const int64_t total = batch * per;
+    CU(h->staging.ensure(total * sizeof(float)));
+    CU(h->batch_out.ensure(batch * rows * sizeof(int32_t)));
+    const bool convert = layout == B200LSAP_COL_MAJOR && rows > 1 && cols > 1;
+    if (convert)
+        CU(h->batch_in.ensure(total * sizeof(float)));
+    n_chunks = (int)std::max<int64_t>(1, std::min<int64_t>(8, batch / 16384));
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    CU(cudaStreamWaitEvent(h->up, h->ev[0], 0));   // earlier work of this handle's stream is done with the buffers
+    CU(cudaStreamWaitEvent(h->down, h->ev[0], 0));
+    for (int k = 0; k < n_chunks; k++)
+    {
+        const int64_t b0 = batch * k / n_chunks, nb = batch * (k + 1) / n_chunks - b0;
+        float* stg = h->staging.as<float>() + b0 * per;
+        CU(cudaMemcpyAsync(stg, a + b0 * per, nb * per * sizeof(float), cudaMemcpyHostToDevice, h->up));
+        CU(cudaEventRecord(h->ev_up[k], h->up));
+        CU(cudaStreamWaitEvent(h->stream, h->ev_up[k], 0));
+        const float* src = stg;
+        if (convert)
+        {
+            float* rm = h->batch_in.as<float>() + b0 * per;
+            k_batch_to_row_major<<<grid_for(h, nb * per, 256 * 4), 256, 0, h->stream>>>(stg, rm, nb, rows, cols);
+            h->launches++;
+            src = rm;
+        }
+        int32_t* out = h->batch_out.as<int32_t>() + b0 * rows;
+        const int rc = run_batch(h, src, nb, rows, cols, opts, out, nullptr, false, k);
+        if (rc)
+            return rc;
+        CU(cudaEventRecord(h->ev_done[k], h->stream));
+        CU(cudaStreamWaitEvent(h->down, h->ev_done[k], 0));
+        CU(cudaMemcpyAsync(row_to_col + b0 * rows, out, nb * rows * sizeof(int32_t), cudaMemcpyDeviceToHost, h->down));
+    }
+    CU(cudaEventRecord(h->ev[3], h->down));
+    return B200LSAP_OK;
+}
+
+int batch_host_wait(b200lsap_handle* h, int64_t batch, int rows, int cols, const b200lsap_options* opts, int n_chunks,
+                    b200lsap_stats* stats)
+{
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->down));
+    CU(cudaStreamWaitEvent(h->stream, h->ev[3], 0)); // later work on the handle's stream follows the downloads
+    CU(cudaGetLastError());
+    if (stats)
+    {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev[0], h->ev[3]);
+        stats->ms_solve = ms; // upload, kernels and download overlap: the whole pipeline
+        b200lsap_options o;
+        b200lsap_options_default(&o);
+        if (opts)
+            o = *opts;
+        stats->eps_final = o.eps_multiplier / (double)cols;
+        stats->bid_bytes = batch * ((int64_t)rows * cols * 4 + rows * 4);
+        stats->launches = h->launches;
+    }
+    return batch_collect(h, 0, n_chunks, stats);
+}
+
+} // namespace
+
+extern "C" {
+
 int b200lsap_solve_batch_f32(b200lsap_handle* h, const float* a, int64_t batch, int32_t rows, int32_t cols, int layout,
                              const b200lsap_options* opts, int32_t* row_to_col, b200lsap_stats* stats)
 {
@@ -1226,38 +1346,16 @@ int b200lsap_solve_batch_f32(b200lsap_handle* h, const float* a, int64_t batch, 
         memset(stats, 0, sizeof *stats);
     if (batch == 0)
         return B200LSAP_OK;
-    CU(cudaSetDevice(h->device));
-    h->launches = 0;
-    const int64_t total = batch * rows * cols;
-    CU(h->staging.ensure(total * sizeof(float)));
-    CU(h->batch_out.ensure(batch * rows * sizeof(int32_t)));
-    CU(cudaEventRecord(h->ev[0], h->stream));
-    CU(cudaMemcpyAsync(h->staging.p, a, total * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    const float* src = h->staging.as<float>();
-    if (layout == B200LSAP_COL_MAJOR && rows > 1 && cols > 1)
-    {
-        CU(h->batch_in.ensure(total * sizeof(float)));
-        k_batch_to_row_major<<<grid_for(h, total, 256 * 4), 256, 0, h->stream>>>(src, h->batch_in.as<float>(), batch,
-                                                                                rows, cols);
-        h->launches++;
-        src = h->batch_in.as<float>();
-    }
-    rc = run_batch(h, src, batch, rows, cols, opts, h->batch_out.as<int32_t>(), stats);
+    int n_chunks = 0;
+    rc = batch_host_enqueue(h, a, batch, rows, cols, layout, opts, row_to_col, n_chunks);
     if (rc)
-        return rc;
-    CU(cudaMemcpyAsync(row_to_col, h->batch_out.p, batch * rows * sizeof(int32_t), cudaMemcpyDeviceToHost,
-                       h->stream));
-    CU(cudaEventRecord(h->ev[3], h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    if (stats)
     {
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]);
-        stats->ms_upload = ms;
-        cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
-        stats->ms_download = ms;
+        cudaStreamSynchronize(h->up);
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->down);
+        return rc;
     }
-    return B200LSAP_OK;
+    return batch_host_wait(h, batch, rows, cols, opts, n_chunks, stats);
 }
 
 int b200lsap_generate_device_f32(b200lsap_handle* h, float* a_dev, int64_t batch, int64_t rows, int64_t cols,
@@ -1767,6 +1865,274 @@ int b200lsap_solve_sharded_device_f32(b200lsap_handle* h, const float* a_dev, in
     if (rc)
         return rc;
     return b200lsap_solve_sharded_end(h, row_to_col_dev, prices_dev, stats);
+}
+
+} // extern "C"
+
+// =============================================================================================
+// Several GPUs from one host thread ("the handle owns device buffers, streams and
+// communicators"): b200lsap_multi owns one handle per device, enables peer access and wires the mailboxes of the
+// fused sharded solve, so a C++ caller of AuctionB200.h reaches the column-sharded and the batch-split mode without
+// torch.distributed or NCCL.
+// =============================================================================================
+struct b200lsap_multi
+{
+    std::vector<b200lsap_handle*> hs;
+    std::vector<int> devices;
+    int64_t rows_cap = 0;
+    std::string err;
+};
+
+namespace
+{
+
+int mfail(b200lsap_multi* m, int status, const std::string& what)
+{
+    if (m)
+        m->err = what;
+    return status;
+}
+
+// (col0, cols_local) per rank: AuctionCommon.h:302-320 (cumulative interval ends, remainder over the first intervals)
+// with boundaries on multiples of 128 columns (512 bytes), or of 4 when there are too few columns for that.
+bool multi_split(int64_t cols, int n, std::vector<std::pair<int64_t, int64_t>>& out)
+{
+    int64_t align = 128, blocks = (cols + align - 1) / align;
+    if (blocks < n)
+    {
+        align = 4;
+        blocks = (cols + 3) / 4;
+        if (blocks < n)
+            return false;
+    }
+    out.clear();
+    int64_t c = 0;
+    for (int r = 0; r < n; r++)
+    {
+        const int64_t nb = blocks / n + (r < blocks % n ? 1 : 0);
+        const int64_t c1 = std::min(cols, c + nb * align);
+        out.push_back({c, c1 - c});
+        c = c1;
+    }
+    return c == cols;
+}
+
+int multi_wire(b200lsap_multi* m, int64_t rows)
+{
+    if (rows <= m->rows_cap)
+        return B200LSAP_OK;
+    const int n = (int)m->hs.size();
+    std::vector<void*> ptrs(n);
+    for (int r = 0; r < n; r++)
+    {
+        const int rc = b200lsap_shard_comm_create(m->hs[r], rows, n, nullptr);
+        if (rc)
+            return mfail(m, rc, b200lsap_last_error(m->hs[r]));
+        ptrs[r] = b200lsap_shard_comm_ptr(m->hs[r]);
+    }
+    for (int r = 0; r < n; r++)
+    {
+        const int share = (int)std::count(m->devices.begin(), m->devices.end(), m->devices[r]);
+        const int rc = b200lsap_shard_comm_connect(m->hs[r], r, n, nullptr, ptrs.data(), share);
+        if (rc)
+            return mfail(m, rc, b200lsap_last_error(m->hs[r]));
+    }
+    m->rows_cap = rows;
+    return B200LSAP_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int b200lsap_create_multi(b200lsap_multi** out, const int* devices, int ndev)
+{
+    if (!out || !devices || ndev < 1 || ndev > kShardMaxRanks)
+        return B200LSAP_ERR_ARG;
+    *out = nullptr;
+    b200lsap_multi* m = new b200lsap_multi();
+    for (int r = 0; r < ndev; r++)
+    {
+        b200lsap_handle* h = nullptr;
+        const int rc = b200lsap_create(&h, devices[r]);
+        if (rc)
+        {
+            for (auto* x : m->hs)
+                b200lsap_destroy(x);
+            delete m;
+            return rc;
+        }
+        m->hs.push_back(h);
+        m->devices.push_back(h->device);
+    }
+    *out = m;
+    return B200LSAP_OK;
+}
+
+int b200lsap_destroy_multi(b200lsap_multi* m)
+{
+    if (!m)
+        return B200LSAP_OK;
+    for (auto* h : m->hs)
+        b200lsap_destroy(h);
+    delete m;
+    return B200LSAP_OK;
+}
+
+const char* b200lsap_multi_last_error(const b200lsap_multi* m) { return m ? m->err.c_str() : "null handle"; }
+
+int b200lsap_multi_devices(const b200lsap_multi* m) { return m ? (int)m->hs.size() : 0; }
+
+int b200lsap_multi_solve_f32(b200lsap_multi* m, const float* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                             const b200lsap_options* opts, int64_t* row_to_col, double* prices_out, b200lsap_stats* stats)
+{
+    if (!m)
+        return B200LSAP_ERR_ARG;
+    if (!a || !row_to_col)
+        return mfail(m, B200LSAP_ERR_ARG, "null pointer");
+    if (layout != B200LSAP_COL_MAJOR && layout != B200LSAP_ROW_MAJOR)
+        return mfail(m, B200LSAP_ERR_ARG, "layout must be 0 or 1");
+    if (rows < 1 || cols < 1 || rows > cols || ld < (layout ? cols : rows))
+        return mfail(m, B200LSAP_ERR_SHAPE, b200lsap_status_string(B200LSAP_ERR_SHAPE));
+    const int n = (int)m->hs.size();
+    std::vector<std::pair<int64_t, int64_t>> parts;
+    if (!multi_split(cols, n, parts))
+        return mfail(m, B200LSAP_ERR_SHAPE, "too few columns to split over the devices in multiples of 4");
+    int rc = multi_wire(m, rows);
+    if (rc)
+        return rc;
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    // upload every rank's column interval (Eigen's column-major: a contiguous block, transposed on the device)
+    std::vector<int64_t> lds(n);
+    for (int r = 0; r < n; r++)
+    {
+        b200lsap_handle* h = m->hs[r];
+        const int64_t c0 = parts[r].first, cl = parts[r].second, ldl = round_up(cl, 4);
+        lds[r] = ldl;
+        if (cudaSetDevice(h->device) != cudaSuccess || h->a.ensure((size_t)rows * ldl * sizeof(float)) != cudaSuccess)
+            return mfail(m, B200LSAP_ERR_CUDA, "device buffer for a shard");
+        cudaError_t e;
+        if (layout == B200LSAP_COL_MAJOR)
+        {
+            e = h->staging.ensure((size_t)cl * rows * sizeof(float));
+            if (e == cudaSuccess)
+                e = cudaMemcpy2DAsync(h->staging.p, rows * sizeof(float), a + c0 * ld, ld * sizeof(float), rows * sizeof(float),
+                                      cl, cudaMemcpyHostToDevice, h->stream);
+            if (e == cudaSuccess)
+                k_transpose_pad<float><<<grid_for(h, rows * ldl, 1024), 256, 0, h->stream>>>(h->staging.as<float>(), rows,
+                                                                                           h->a.as<float>(), ldl, (int)rows, (int)cl);
+        }
+        else
+        {
+            e = cudaMemsetAsync(h->a.p, 0, (size_t)rows * ldl * sizeof(float), h->stream);
+            if (e == cudaSuccess)
+                e = cudaMemcpy2DAsync(h->a.p, ldl * sizeof(float), a + c0, ld * sizeof(float), cl * sizeof(float), rows,
+                                      cudaMemcpyHostToDevice, h->stream);
+        }
+        if (e != cudaSuccess)
+            return mfail(m, B200LSAP_ERR_CUDA, std::string("shard upload: ") + cudaGetErrorString(e));
+        rc = b200lsap_shard_reserve(h, rows, cols); // before any rank's kernel is waiting for its peers
+        if (rc)
+            return mfail(m, rc, b200lsap_last_error(h));
+    }
+    for (int r = 0; r < n; r++)
+    {
+        rc = b200lsap_solve_sharded_begin_f32(m->hs[r], m->hs[r]->a.as<float>(), rows, parts[r].second, lds[r],
+                                              parts[r].first, cols, opts);
+        if (rc)
+        {
+            // ranks already started give up at the spin limit; collect them so that the handles stay usable
+            for (int q = 0; q < r; q++)
+                b200lsap_solve_sharded_end(m->hs[q], nullptr, nullptr, nullptr);
+            m->rows_cap = 0;
+            return mfail(m, rc, b200lsap_last_error(m->hs[r]));
+        }
+    }
+    int first_rc = B200LSAP_OK;
+    for (int r = 0; r < n; r++)
+    {
+        b200lsap_stats st;
+        rc = b200lsap_solve_sharded_end(m->hs[r], nullptr, nullptr, &st);
+        if (rc && !first_rc)
+        {
+            first_rc = rc;
+            m->err = b200lsap_last_error(m->hs[r]);
+        }
+        if (r == 0 && stats)
+            *stats = st;
+        else if (stats)
+            stats->ms_solve = std::max(stats->ms_solve, st.ms_solve);
+    }
+    if (first_rc)
+    {
+        if (first_rc == B200LSAP_ERR_CUDA)
+            m->rows_cap = 0; // wire the mailboxes again next time
+        return first_rc;
+    }
+    // every rank holds the same assignment and prices: rank 0's replica goes back to the caller
+    b200lsap_handle* h = m->hs[0];
+    if (cudaSetDevice(h->device) != cudaSuccess || h->out64.ensure(rows * sizeof(long long)) != cudaSuccess)
+        return mfail(m, B200LSAP_ERR_CUDA, "result buffer");
+    k_widen_i32<<<grid_for(h, rows, 256), 256, 0, h->stream>>>(h->row2col.as<int>(), h->out64.as<long long>(), rows);
+    cudaMemcpyAsync(row_to_col, h->out64.p, rows * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream);
+    if (prices_out)
+        cudaMemcpyAsync(prices_out, h->prices.p, cols * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess)
+        return mfail(m, B200LSAP_ERR_CUDA, "result download");
+    return B200LSAP_OK;
+}
+
+int b200lsap_multi_solve_batch_f32(b200lsap_multi* m, const float* a, int64_t batch, int32_t rows, int32_t cols,
+                                   int layout, const b200lsap_options* opts, int32_t* row_to_col, b200lsap_stats* stats)
+{
+    if (!m)
+        return B200LSAP_ERR_ARG;
+    const int n = (int)m->hs.size();
+    int rc = check_batch(m->hs[0], a, batch, rows, cols, layout, row_to_col);
+    if (rc)
+        return mfail(m, rc, b200lsap_last_error(m->hs[0]));
+    if (stats)
+        memset(stats, 0, sizeof *stats);
+    if (batch == 0)
+        return B200LSAP_OK;
+    // contiguous slices of the batch, one per device; every device runs its own upload / kernel / download pipeline
+    std::vector<int> chunks(n, 0);
+    const int64_t per = (int64_t)rows * cols;
+    int first_rc = B200LSAP_OK;
+    for (int r = 0; r < n && !first_rc; r++)
+    {
+        const int64_t b0 = batch * r / n, nb = batch * (r + 1) / n - b0;
+        if (nb == 0)
+            continue;
+        first_rc = batch_host_enqueue(m->hs[r], a + b0 * per, nb, rows, cols, layout, opts, row_to_col + b0 * rows, chunks[r]);
+        if (first_rc)
+            m->err = b200lsap_last_error(m->hs[r]);
+    }
+    for (int r = 0; r < n; r++)
+    {
+        const int64_t b0 = batch * r / n, nb = batch * (r + 1) / n - b0;
+        if (nb == 0 || chunks[r] == 0)
+            continue;
+        b200lsap_stats st;
+        memset(&st, 0, sizeof st);
+        rc = batch_host_wait(m->hs[r], nb, rows, cols, opts, chunks[r], &st);
+        if (rc && !first_rc)
+        {
+            first_rc = rc;
+            m->err = b200lsap_last_error(m->hs[r]);
+        }
+        if (stats)
+        {
+            stats->ms_solve = std::max(stats->ms_solve, st.ms_solve);
+            stats->bid_bytes += st.bid_bytes;
+            stats->launches += st.launches;
+            stats->batch_takeovers += st.batch_takeovers;
+            stats->batch_max_bids = std::max(stats->batch_max_bids, st.batch_max_bids);
+            stats->eps_final = st.eps_final;
+        }
+    }
+    return first_rc;
 }
 
 } // extern "C"

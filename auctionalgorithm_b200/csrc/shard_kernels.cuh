@@ -288,29 +288,31 @@ __device__ __forceinline__ bool shard_exchange(const ShardComm& cm, unsigned lon
 // several waves: the S that minimises waves(n * S) * (row time / S + item overhead), with a warp streaming
 // ~1.7 GB/s (four 512-byte pieces in flight per ~1.2 us of latency) and ~3 us per item for the partial result, the
 // fence and the ticket.
-// (Measured on 65536 x 98304, one GPU: 10.9 ms with this rule against 9.4-9.8 ms with split_factor's powers of two:
-// the split-row path costs more per item than the model assumes.  Kept for experiments, off by default.)
+// (Measured on 65536 x 98304, one GPU: 9.4-9.5 ms with this rule, 10.9 ms with any integer S and a per-item cost in
+// microseconds, against 9.3 ms with split_factor's powers of two: the split-row path (partial result, fence, ticket)
+// costs more per item than these models assume.  Kept for experiments, off by default.)
 #ifndef B200LSAP_SHARD_SPLIT_MODEL
 #define B200LSAP_SHARD_SPLIT_MODEL 0
 #endif
 constexpr bool kShardSplitModel = B200LSAP_SHARD_SPLIT_MODEL != 0;
 __device__ __forceinline__ int shard_split(int n, int n_warps, int cols4, int min_seg, long long cap_items)
 {
-    int s_max = min(128, max(1, cols4 / max(min_seg, 128)));
+    int s_max = max(1, cols4 / max(min_seg, 128));
     s_max = (int)min((long long)s_max, max(1ll, cap_items / n));
-    const float t_row = (float)cols4 * (4.0f / 1700.0f), t_item = 3.0f; // microseconds
+    // S from {1, 2, 3, 4, 6, 8, 12, ...}: powers of two and their 1.5-fold; cost in whole-row scans, 2 % per item
     int best = 1;
-    float best_cost = (float)((n + n_warps - 1) / n_warps) * t_row;
-    for (int s = 2; s <= s_max; s++)
-    {
-        const long long items = (long long)n * s;
-        const float cost = (float)((items + n_warps - 1) / n_warps) * (t_row / (float)s + t_item);
-        if (cost < 0.97f * best_cost)
+    float best_cost = (float)((n + n_warps - 1) / n_warps) * 1.02f;
+    for (int base = 2; base <= s_max && base <= 128; base *= 2)
+        for (int s = base; s <= base + base / 2 && s <= s_max; s += max(1, base / 2))
         {
-            best = s;
-            best_cost = cost;
+            const long long items = (long long)n * s;
+            const float cost = (float)((items + n_warps - 1) / n_warps) * (1.0f / (float)s + 0.02f);
+            if (cost < 0.97f * best_cost)
+            {
+                best = s;
+                best_cost = cost;
+            }
         }
-    }
     return best;
 }
 

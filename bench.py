@@ -498,9 +498,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     torch.cuda.set_device(local)
     if world > 1:
-        # rank 0 prints ONE JSON line on stdout: keep NCCL's version banner off it
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # rank 0 prints ONE JSON line on stdout: whatever NCCL logs (version banner included) goes to a file
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nccl.%h.%p.log")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     handle = ab.Handle(local)
     handle.set_stream(torch.cuda.current_stream().cuda_stream)

@@ -201,6 +201,61 @@ public:
     }
 };
 
+/* The same solve with the matrix column-sharded over several GPUs of this machine (AuctionMT's column intervals,
+ * AuctionMT.h:76-77, with a GPU per interval and one in-kernel exchange per round; b200lsap_multi_solve_f32).
+ * fp32 matrices.  devices: CUDA device ids, one rank each (an id may repeat).  The b200lsap_multi is built on first
+ * use and kept per host thread for the same device list.
+ *
+ *   Auction<float, Eigen::MatrixXf>::Edges e = LSAP::AuctionShardedB200<float>::solve(m, {0, 1, 2, 3});
+ */
+template <typename Scalar = float, typename MatrixType = void> class AuctionShardedB200
+{
+public:
+    typedef typename B200Types<Scalar>::Edge Edge;
+    typedef typename B200Types<Scalar>::Edges Edges;
+
+    template <typename M>
+    static Edges solve(const M& a, const std::vector<int>& devices, const b200lsap_options* opts = nullptr,
+                       b200lsap_stats* stats = nullptr)
+    {
+        static_assert(sizeof(Scalar) == 4, "the column-sharded solve takes fp32 matrices");
+        struct Holder
+        {
+            b200lsap_multi* m = nullptr;
+            std::vector<int> devices;
+            ~Holder() { b200lsap_destroy_multi(m); }
+        };
+        static thread_local Holder holder;
+        if (!holder.m || holder.devices != devices)
+        {
+            b200lsap_destroy_multi(holder.m);
+            holder.m = nullptr;
+            const int rc = b200lsap_create_multi(&holder.m, devices.data(), (int)devices.size());
+            if (rc != B200LSAP_OK)
+                throw std::runtime_error(std::string("b200lsap_create_multi: ") + b200lsap_status_string(rc));
+            holder.devices = devices;
+        }
+        const int64_t rows = (int64_t)a.rows(), cols = (int64_t)a.cols();
+        Edges E;
+        if (rows == 0 || cols == 0)
+            return E;
+        std::vector<int64_t> row_to_col((size_t)rows, -1);
+        const int layout = M::IsRowMajor ? B200LSAP_ROW_MAJOR : B200LSAP_COL_MAJOR;
+        const int rc = b200lsap_multi_solve_f32(holder.m, a.data(), rows, cols, (int64_t)a.outerStride(), layout, opts,
+                                                row_to_col.data(), nullptr, stats);
+        if (rc != B200LSAP_OK)
+            throw std::runtime_error(std::string("AuctionShardedB200::solve: ") + b200lsap_multi_last_error(holder.m));
+        E.resize((size_t)rows);
+        for (int64_t i = 0; i < rows; ++i)
+        {
+            E[(size_t)i].x = (size_t)i;
+            E[(size_t)i].y = (size_t)row_to_col[(size_t)i];
+            E[(size_t)i].v = a(i, row_to_col[(size_t)i]); /* from the caller's matrix: Auction.h:273,283 */
+        }
+        return E;
+    }
+};
+
 } // namespace LSAP
 
 #endif /* AUCTION_B200_H_ */

@@ -265,6 +265,30 @@ int b200lsap_solve_sharded_device_f32(b200lsap_handle* handle, const float* a_de
                                       int64_t ld, int64_t col0, int64_t cols_global, const b200lsap_options* opts,
                                       int32_t* row_to_col_dev, double* prices_dev, b200lsap_stats* stats);
 
+/*
+ * Several GPUs from ONE host thread.  b200lsap_multi owns a handle per device (devices[] may name a device more
+ * than once: several ranks then share it), enables peer access between them and wires the mailboxes of the fused
+ * sharded solve, so the column-sharded and the batch-split mode need neither NCCL nor torch.distributed:
+ *     multi_solve_f32        Auction<Scalar>::solve / AuctionMT<Scalar>::solve (Auction.h:44, AuctionMT.h:50) on a
+ *                            HOST matrix, column intervals over the devices (AuctionMT.h:76-77,
+ *                            AuctionCommon.h:302-320), one in-kernel exchange per round; same result as
+ *                            b200lsap_solve_f32 with wide rounds only (identical prices)
+ *     multi_solve_batch_f32  b200lsap_solve_batch_f32 with the batch cut into contiguous slices, one per device,
+ *                            every device running its own upload / kernel / download pipeline
+ * Arguments as in the single-device entries.  Errors: the status is returned, the text is in multi_last_error.
+ */
+typedef struct b200lsap_multi b200lsap_multi;
+int b200lsap_create_multi(b200lsap_multi** multi, const int* devices, int ndev);
+int b200lsap_destroy_multi(b200lsap_multi* multi);
+const char* b200lsap_multi_last_error(const b200lsap_multi* multi);
+int b200lsap_multi_devices(const b200lsap_multi* multi);
+int b200lsap_multi_solve_f32(b200lsap_multi* multi, const float* a, int64_t rows, int64_t cols, int64_t ld, int layout,
+                             const b200lsap_options* opts, int64_t* row_to_col, double* prices_out,
+                             b200lsap_stats* stats);
+int b200lsap_multi_solve_batch_f32(b200lsap_multi* multi, const float* a, int64_t batch, int32_t rows, int32_t cols,
+                                   int layout, const b200lsap_options* opts, int32_t* row_to_col,
+                                   b200lsap_stats* stats);
+
 /* Full-sweep bidding pass for measurement: every row bids once, nothing is updated.
  * use_last_prices = 0: the state a solve starts from (zero prices, no candidate lists: the first
  * sweep of the first eps phase).  1: the state the handle's last dense solve left: its prices and,

@@ -18,7 +18,7 @@ class Options(C.Structure):
     _fields_ = [("eps_multiplier", C.c_double), ("eps_scaling", C.c_int32), ("eps_start", C.c_double),
                 ("eps_factor", C.c_double), ("max_rounds", C.c_int64), ("driver", C.c_int32),
                 ("tail_rows", C.c_int32), ("narrow_rows", C.c_int32), ("row_cache", C.c_int32),
-                ("batch_bid_cap", C.c_int32)]
+                ("batch_bid_cap", C.c_int32), ("prices_in", C.c_void_p)]
 
 
 class Stats(C.Structure):
@@ -26,7 +26,8 @@ class Stats(C.Structure):
                 ("eps_final", C.c_double), ("ms_upload", C.c_double), ("ms_solve", C.c_double),
                 ("ms_download", C.c_double), ("launches", C.c_int64), ("tail_bids", C.c_int64), ("tail_runs", C.c_int64),
                 ("narrow_rounds", C.c_int64), ("cache_hits", C.c_int64), ("cache_misses", C.c_int64),
-                ("eps_first", C.c_double), ("batch_takeovers", C.c_int64), ("batch_max_bids", C.c_int64)]
+                ("eps_first", C.c_double), ("batch_takeovers", C.c_int64), ("batch_max_bids", C.c_int64),
+                ("warm_fallback", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}

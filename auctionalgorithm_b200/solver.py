@@ -62,7 +62,8 @@ class Handle:
 
     @staticmethod
     def _opts(eps_multiplier=None, eps_scaling=None, eps_start=None, eps_factor=None, max_rounds=None,
-              driver=None, tail_rows=None, narrow_rows=None, row_cache=None, batch_bid_cap=None) -> Options:
+              driver=None, tail_rows=None, narrow_rows=None, row_cache=None, batch_bid_cap=None,
+              prices_in=None) -> Options:
         o = Options()
         _capi.lib().b200lsap_options_default(C.byref(o))
         if eps_multiplier is not None:
@@ -85,6 +86,14 @@ class Handle:
             o.narrow_rows = narrow_rows
         if batch_bid_cap is not None:
             o.batch_bid_cap = batch_bid_cap
+        if prices_in is not None:
+            # warm start: a float64 numpy array (host entries; kept alive on the Options object) or a raw device
+            # pointer (device entries)
+            if isinstance(prices_in, np.ndarray):
+                o._prices_keepalive = np.ascontiguousarray(prices_in, np.float64)
+                o.prices_in = o._prices_keepalive.ctypes.data
+            else:
+                o.prices_in = int(prices_in)
         return o
 
     def set_stream(self, cuda_stream: int):

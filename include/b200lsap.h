@@ -84,6 +84,19 @@ typedef struct
                               lanes to its whole warp, which continues the same Gauss-Seidel sweep ~5x faster
                               per bid (same bids, same result; it only bounds how long a price war can hold
                               a launch).  0: default (96), -1: never */
+    const double* prices_in; /* warm start of the dense solve (b200lsap_solve_f32/_f64 and their _device variants): cols
+                              object prices to start from instead of zeros (Auction.h:58) — e.g. the prices_out of the
+                              previous frame of a tracker.  Host memory for the host entries, device memory for the
+                              _device entries.  Non-negative, finite.  Every row still starts unassigned, so the result
+                              satisfies eps-complementary slackness at eps_multiplier / cols exactly as a cold solve
+                              does (same assignment whenever the optimum is unique by more than rows * eps).  The eps
+                              schedule is kept (its first eps is sized at the imported prices): measured, a frame whose
+                              coefficients moved a little takes 10-30 % fewer rounds than a cold solve; eps_scaling = 0
+                              (one phase at the final eps) only pays when the prices are already this matrix's
+                              equilibrium.  rows < cols: the
+                              post-condition "no unassigned column is priced above an assigned one"
+                              (AuctionCommon.h:347-354) is checked afterwards and the solve repeated from zero prices
+                              when the imported prices break it (stats.warm_fallback).  NULL: cold start. */
 } b200lsap_options;
 
 typedef struct
@@ -108,6 +121,7 @@ typedef struct
     double eps_first;      /* eps of the first phase */
     int64_t batch_takeovers; /* batched mode: problems that reached batch_bid_cap and were finished by a warp */
     int64_t batch_max_bids;  /* batched mode: largest bid count of a problem (filtered kernel) */
+    int64_t warm_fallback;   /* 1: a warm-started asymmetric solve broke the price post-condition and was repeated cold */
 } b200lsap_stats;
 
 /* device < 0: the current CUDA device.  Creates the handle's own non-blocking stream. */

@@ -30,7 +30,7 @@ def test_header_symbols_are_exported(ab):
 def test_struct_sizes(ab):
     import ctypes as C
     from auctionalgorithm_b200._capi import Options, Stats
-    assert C.sizeof(Options) == 64 and C.sizeof(Stats) == 9 * 8 + 48 + 16
+    assert C.sizeof(Options) == 72 and C.sizeof(Stats) == 9 * 8 + 48 + 24
     o = Options()
     ab.lib().b200lsap_options_default(C.byref(o))
     assert o.eps_multiplier == 1e-5 and o.eps_scaling == -1 and o.driver == 0

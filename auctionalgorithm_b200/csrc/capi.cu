@@ -366,6 +366,66 @@ __global__ void __launch_bounds__(256) k_lambda_check(const double* __restrict__
     atomicMin(&out[1], (unsigned long long)__double_as_longlong(lo));
 }
 
+// Continuation of a finished solve: the unassigned rows become the bidders of the last eps phase again.
+// pass 0 (one thread): counters; pass 1 (grid): compaction.
+template <typename T> __global__ void __launch_bounds__(kThreads, 1) k_resume(DenseState<T> s, int pass)
+{
+    DenseCtrl* c = s.ctrl;
+    if (pass == 0)
+    {
+        c->count[0] = c->count[1] = 0;
+        c->done = 0;
+        c->phase = c->n_phases - 1;
+        c->phase_work = 0;
+        c->phase_budget = 0;
+        s.narrow->arrived = 0u; // the scanner hand-shake of the row-scanning path starts from scratch, as after k_init
+        return;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < kNarrowMax)
+        s.narrow->slot[threadIdx.x].flag = 0;
+    const int cur = c->cur, lane = threadIdx.x & 31;
+    const long long n_threads = (long long)gridDim.x * blockDim.x;
+    const long long up = ((long long)s.rows + 31) & ~31ll;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < up; i += n_threads)
+    {
+        const bool push = i < s.rows && s.row2col[i] < 0;
+        const unsigned m = __ballot_sync(kFullMask, push);
+        if (m)
+        {
+            int base = 0;
+            if (lane == 0)
+                base = atomicAdd(&c->count[cur], __popc(m));
+            base = __shfl_sync(kFullMask, base, 0);
+            if (push)
+                s.list[cur][base + __popc(m & ((1u << lane) - 1))] = (int)i;
+        }
+    }
+}
+
+// The collective move of the cols - rows "dummy bidders" that make an asymmetric problem square (each values every
+// object the same, so it only ever wants the cheapest one): every price below `floor` rises to `floor`, and a row
+// whose object was raised is unassigned and bids again.  Prices only go up, so every bound the scans keep (candidate
+// lists, row caches, bid slots) stays valid; the rows that keep their object keep eps-CS (the others' prices rose).
+// This is what the reference's reverse auction is for (Auction.h:346-469, lambda raised at :436-464), done from the
+// side that keeps prices monotone.
+__global__ void __launch_bounds__(256) k_floor_raise(double* __restrict__ prices, float* __restrict__ pricesf,
+                                                     int* __restrict__ owner, int* __restrict__ row2col, long long cols,
+                                                     double floor)
+{
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < cols; j += (long long)gridDim.x * blockDim.x)
+        if (prices[j] < floor)
+        {
+            prices[j] = floor;
+            pricesf[j] = (float)floor;
+            const int o = owner[j];
+            if (o >= 0)
+            {
+                row2col[o] = -1;
+                owner[j] = -1;
+            }
+        }
+}
+
 // owner[] as the inverse of the returned assignment (the narrow-round kernels keep their own copy while they run).
 __global__ void __launch_bounds__(256) k_owner_from_assignment(const int* __restrict__ row2col, long long rows, long long cols,
                                                                int* __restrict__ owner, int pass)
@@ -395,10 +455,8 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
     // against 6 582 cold: imported prices save the price DISCOVERY of the early phases, not the phases themselves)
     bool scaling = o.eps_scaling < 0 ? (rows == cols) : (o.eps_scaling != 0);
     plan.prices_in = o.prices_in;
-    if (scaling && rows != cols)
-        return fail(h, B200LSAP_ERR_ARG,
-                    "eps scaling needs rows == cols: a forward-only auction with scaled eps is not optimal on "
-                    "asymmetric problems (SURVEY.md section 7.3)");
+    if (scaling && rows != cols && o.driver != 0)
+        return fail(h, B200LSAP_ERR_ARG, "eps scaling on rows < cols needs the persistent driver (driver = 0)");
     plan.eps.clear();
     plan.eps_auto = scaling && !(o.eps_start > 0);
     plan.eps_factor = o.eps_factor > 1 ? o.eps_factor : 7.0;
@@ -480,6 +538,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.tail_rows = 0;
     s.dry = 0;
     s.narrow_after = 0;
+    s.phase_cut = 0;
     return s;
 }
 
@@ -496,7 +555,10 @@ template <typename T> int persistent_grid(b200lsap_handle* h, int& grid)
 // Runs the auction on a padded row-major device matrix.  On return h->row2col holds the
 // assignment and h->h_ctrl the controller block.
 template <typename T>
-int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan, b200lsap_stats* stats)
+// resume: the state of the solve that has just finished on this handle is kept (prices, owners, caches); the rows
+// that the caller has unassigned since (k_floor_raise) bid again in the LAST eps phase until every row is assigned.
+int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan, b200lsap_stats* stats,
+                   bool resume = false)
 {
     int grid = 0;
     int rc = persistent_grid<T>(h, grid);
@@ -511,13 +573,31 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
     s.narrow_rows = plan.narrow_rows;
 
     DenseCtrl* hc = h->h_ctrl;
+    const bool eps_auto = plan.eps_auto && !resume;
+    s.use_cache = (plan.driver == 0 && plan.use_cache) ? 1 : 0;
+    {
+        // the cache-building sweep reads the matrix once (~6.5 TB/s); a small wide round costs ~20 us
+        const double sweep_us = (double)plan.rows * (double)ld * sizeof(T) / 6.5e6;
+        s.narrow_after = sweep_us > 1000.0 ? (int)std::min(1e6, sweep_us / 20.0) : 0;
+    }
+    if (const char* e = getenv("B200LSAP_PHASE_CUT"))
+        s.phase_cut = plan.driver == 0 ? atoi(e) : 0;
+    std::vector<double> eps = plan.eps;
+    if (resume)
+    {
+        eps.assign(1, plan.eps.back());
+        k_resume<T><<<1, 1, 0, h->stream>>>(s, 0);
+        k_resume<T><<<grid, kThreads, 0, h->stream>>>(s, 1);
+        h->launches += 2;
+    }
+    else
+    {
     memset(hc, 0, sizeof *hc);
     hc->count[0] = (int)plan.rows;
     hc->n_phases = (int)plan.eps.size();
     hc->max_rounds = plan.max_rounds;
     for (size_t k = 0; k < plan.eps.size(); k++)
         hc->eps[k] = plan.eps[k];
-    const bool eps_auto = plan.eps_auto;
     hc->eps_auto = eps_auto ? 1 : 0;
     hc->eps_factor = plan.eps_factor;
     hc->eps_final = plan.eps.back();
@@ -525,13 +605,6 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
     hc->eps_cap = 0.25;
     hc->phase_budget = eps_auto ? 4 * plan.rows + 1024 : 0;
     CU(cudaMemcpyAsync(s.ctrl, hc, sizeof *hc, cudaMemcpyHostToDevice, h->stream));
-    s.use_cache = (plan.driver == 0 && plan.use_cache) ? 1 : 0;
-    {
-        // the cache-building sweep reads the matrix once (~6.5 TB/s); a small wide round costs ~20 us
-        const double sweep_us = (double)plan.rows * (double)ld * sizeof(T) / 6.5e6;
-        s.narrow_after = sweep_us > 1000.0 ? (int)std::min(1e6, sweep_us / 20.0) : 0;
-    }
-    std::vector<double> eps = plan.eps;
 
     CU(cudaEventRecord(h->ev[1], h->stream));
     if (plan.prices_in)
@@ -565,6 +638,7 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
                 eps.assign(hc->eps, hc->eps + hc->n_phases);
             }
         }
+    }
     }
     if (plan.driver == 0)
     {
@@ -694,42 +768,62 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
     return B200LSAP_OK;
 }
 
-// A warm-started asymmetric solve must still end with every unassigned column priced no higher than any assigned
-// one; when the imported prices break that (they belonged to a too different matrix), the solve is repeated cold.
+// rows < cols with eps scaling or a warm start: a forward auction alone may end with an unassigned object priced above
+// an assigned one, which breaks the post-condition of AuctionCommon.h:347-354 and with it optimality.  The repair is
+// the reverse auction's job in the reference (Auction.h:346-469); here: raise every price below the highest
+// unassigned price F to F (k_floor_raise: prices stay monotone), unassign the rows whose object was raised, let them
+// bid again at the final eps, and repeat until the condition holds.  Every iteration raises the floor, so it ends.
 template <typename T>
 int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan, b200lsap_stats* stats)
 {
     int rc = run_dense_once<T>(h, A, ld, plan, stats);
-    if (rc || !plan.prices_in || plan.rows == plan.cols)
-        return rc;
-    CU(h->out64.ensure(2 * sizeof(unsigned long long)));
-    unsigned long long init[2] = {0ull, (unsigned long long)__builtin_bit_cast(long long, 1e300)};
-    CU(cudaMemcpyAsync(h->out64.p, init, sizeof init, cudaMemcpyHostToDevice, h->stream));
-    for (int pass = 0; pass < 2; pass++)
-        k_owner_from_assignment<<<grid_for(h, plan.cols, 256), 256, 0, h->stream>>>(h->row2col.as<int>(), plan.rows, plan.cols,
-                                                                                 h->owner.as<int>(), pass);
-    k_lambda_check<<<grid_for(h, plan.cols, 256), 256, 0, h->stream>>>(h->prices.as<double>(), h->owner.as<int>(), plan.cols,
-                                                                    h->out64.as<unsigned long long>());
-    unsigned long long got[2];
-    CU(cudaMemcpyAsync(got, h->out64.p, sizeof got, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    h->launches++;
-    if (got[0] <= got[1])
-        return B200LSAP_OK;
-    DensePlan cold = plan;
-    cold.prices_in = nullptr;
-    b200lsap_stats warm;
-    if (stats)
-        warm = *stats;
-    rc = run_dense_once<T>(h, A, ld, cold, stats);
-    if (stats)
+    if (rc || plan.rows == plan.cols || (!plan.prices_in && plan.eps.size() == 1))
+        return rc; // square, or a cold fixed-eps solve: unassigned objects were never priced
+    int64_t repairs = 0;
+    for (int it = 0; it < 1000; it++)
     {
-        stats->warm_fallback = 1;
-        stats->ms_solve += warm.ms_solve;
-        stats->rounds += warm.rounds;
-        stats->bids += warm.bids;
+        CU(h->out64.ensure(2 * sizeof(unsigned long long)));
+        unsigned long long init[2] = {0ull, (unsigned long long)__builtin_bit_cast(long long, 1e300)};
+        CU(cudaMemcpyAsync(h->out64.p, init, sizeof init, cudaMemcpyHostToDevice, h->stream));
+        for (int pass = 0; pass < 2; pass++)
+            k_owner_from_assignment<<<grid_for(h, plan.cols, 256), 256, 0, h->stream>>>(h->row2col.as<int>(), plan.rows,
+                                                                                     plan.cols, h->owner.as<int>(), pass);
+        k_lambda_check<<<grid_for(h, plan.cols, 256), 256, 0, h->stream>>>(h->prices.as<double>(), h->owner.as<int>(),
+                                                                        plan.cols, h->out64.as<unsigned long long>());
+        unsigned long long got[2];
+        CU(cudaMemcpyAsync(got, h->out64.p, sizeof got, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        h->launches += 3;
+        if (got[0] <= got[1])
+            break; // max price of an unassigned object <= min price of an assigned one
+        if (plan.driver != 0)
+            return fail(h, B200LSAP_ERR_ARG, "eps scaling / warm start on rows < cols needs the persistent driver (driver = 0)");
+        const double floor = __builtin_bit_cast(double, (long long)got[0]);
+        k_floor_raise<<<grid_for(h, plan.cols, 256), 256, 0, h->stream>>>(h->prices.as<double>(), h->pricesf.as<float>(),
+                                                                       h->owner.as<int>(), h->row2col.as<int>(), plan.cols,
+                                                                       floor);
+        h->launches++;
+        repairs++;
+        b200lsap_stats more;
+        memset(&more, 0, sizeof more);
+        rc = run_dense_once<T>(h, A, ld, plan, &more, true);
+        if (stats)
+        {
+            stats->ms_solve = more.ms_solve; // ev[1] of the first run .. ev[2] of the last
+            stats->rounds = more.rounds;     // the controller block keeps counting
+            stats->bids = more.bids;
+            stats->narrow_rounds = more.narrow_rounds;
+            stats->tail_bids = more.tail_bids;
+            stats->cache_hits = more.cache_hits;
+            stats->cache_misses = more.cache_misses;
+            stats->bid_bytes = more.bid_bytes;
+        }
+        if (rc)
+            return rc;
     }
-    return rc;
+    if (stats)
+        stats->warm_fallback = repairs;
+    return B200LSAP_OK;
 }
 
 int check_shape(b200lsap_handle* h, const void* a, int64_t rows, int64_t cols, int64_t ld, int layout)

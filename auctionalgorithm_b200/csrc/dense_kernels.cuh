@@ -1035,7 +1035,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
     for (;;)
     {
         const int n = ctrl->count[cur];
-        if (n == 0)
+        if (n == 0 || (n <= s.phase_cut && phase >= 0 && phase + 1 < n_phases))
         {
             if (phase + 1 >= n_phases)
                 break;

@@ -154,6 +154,8 @@ template <typename T> struct DenseState
     CacheEnt<T>* cache;    // [rows][kCacheK] (column, a), best first
     RowCacheHdr* cache_hdr; // [rows]
     int use_cache;         // 1: narrow rounds answer from the row cache (persistent driver)
+    int phase_cut;         // an eps phase other than the last ends as soon as at most this many rows are unassigned
+                           // (the next phase drops every assignment anyway; only the last phase decides the result)
     int narrow_after;      // row caches: a phase plays this many of its small rounds as wide rounds before it pays for
                            // the cache-building sweep (a pass over the whole matrix: 4 ms at 65536 x 98304, where a
                            // random asymmetric problem has ~50 small rounds of ~20 us left); 0: hand over at once

@@ -61,7 +61,13 @@ typedef struct b200lsap_handle b200lsap_handle;
 typedef struct
 {
     double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
-    int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on */
+    int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on.  On with
+                              rows < cols (persistent driver only): after the last phase the post-condition of
+                              AuctionCommon.h:347-354 — no unassigned object priced above an assigned one, what the
+                              reference's reverse auction and lambda are for (Auction.h:346-469) — is restored by
+                              raising every price below the highest unassigned price to it (prices stay monotone),
+                              unassigning the rows whose object was raised and letting them bid again at the final
+                              eps, until it holds (stats.warm_fallback = number of such repairs) */
     double eps_start;      /* first eps of the scaling schedule; <= 0: default (an eighth of the mean spread
                               of a row's best ~36 values, measured on 128 sampled rows, at most 0.25).
                               A default first phase that runs over its work budget
@@ -93,10 +99,9 @@ typedef struct
                               schedule is kept (its first eps is sized at the imported prices): measured, a frame whose
                               coefficients moved a little takes 10-30 % fewer rounds than a cold solve; eps_scaling = 0
                               (one phase at the final eps) only pays when the prices are already this matrix's
-                              equilibrium.  rows < cols: the
-                              post-condition "no unassigned column is priced above an assigned one"
-                              (AuctionCommon.h:347-354) is checked afterwards and the solve repeated from zero prices
-                              when the imported prices break it (stats.warm_fallback).  NULL: cold start. */
+                              equilibrium.  rows < cols: the post-condition "no unassigned column is priced above an
+                              assigned one" (AuctionCommon.h:347-354) is restored afterwards as for eps scaling on
+                              asymmetric problems (eps_scaling above; stats.warm_fallback).  NULL: cold start. */
 } b200lsap_options;
 
 typedef struct
@@ -121,7 +126,8 @@ typedef struct
     double eps_first;      /* eps of the first phase */
     int64_t batch_takeovers; /* batched mode: problems that reached batch_bid_cap and were finished by a warp */
     int64_t batch_max_bids;  /* batched mode: largest bid count of a problem (filtered kernel) */
-    int64_t warm_fallback;   /* 1: a warm-started asymmetric solve broke the price post-condition and was repeated cold */
+    int64_t warm_fallback;   /* rows < cols with eps scaling or a warm start: floor-raise repairs of the price
+                                post-condition (AuctionCommon.h:347-354) after the last phase; 0 = it held at once */
 } b200lsap_stats;
 
 /* device < 0: the current CUDA device.  Creates the handle's own non-blocking stream. */

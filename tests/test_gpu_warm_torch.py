@@ -34,8 +34,7 @@ def test_warm_start_equals_cold_solve(handle, oracle_lib, rows, cols):
         assert st["warm_fallback"] == 0
         assert st["rounds"] <= cold_rounds * 1.1, (st["rounds"], cold_rounds)   # measured: 10-30 % fewer
     # rows < cols: a column that frame 1 priced and frame 2 leaves unassigned breaks the post-condition of
-    # AuctionCommon.h:347-354, which a forward-only auction cannot repair: the solve is then repeated cold
-    # (stats.warm_fallback); either way the answer above is the cold solve's
+    # AuctionCommon.h:347-354; the floor-raise repair (stats.warm_fallback counts its iterations) restores it
     # the same matrix again from its own final prices, one phase at the final eps: hardly anything left to bid for
     again, _ = handle.solve(a2, want_prices=True, prices_in=pw, eps_scaling=0)
     assert np.array_equal(again, cold)
@@ -44,15 +43,15 @@ def test_warm_start_equals_cold_solve(handle, oracle_lib, rows, cols):
         assert handle.last_stats["rounds"] <= max(40, cold_rounds // 10), handle.last_stats["rounds"]
 
 
-def test_warm_start_with_hostile_prices_on_an_asymmetric_problem_falls_back(handle, oracle_lib):
+def test_warm_start_with_hostile_prices_on_an_asymmetric_problem_is_repaired(handle, oracle_lib):
     # prices that belong to nothing: the forward auction still ends with eps-CS, but unassigned columns may stay
-    # priced above assigned ones (AuctionCommon.h:347-354 would not hold): detected, solved again from zero prices
+    # priced above assigned ones (AuctionCommon.h:347-354 would not hold): detected and repaired by the floor raise
     rows, cols = 200, 300
     a = oracle_lib.generate(rows, cols, 2)
     g = np.load(f"{parity.GOLDEN_DIR}/auction_200x300_s2.npz")
     bad = np.random.default_rng(1).random(cols) * 0.9
     r2c, prices = handle.solve(a, want_prices=True, prices_in=bad)
-    assert handle.last_stats["warm_fallback"] == 1
+    assert handle.last_stats["warm_fallback"] >= 1
     assert parity.check_parity(a, r2c, prices, parity.golden_row_to_col(g), 1e-5 / cols) == "exact"
     import auctionalgorithm_b200 as ab
     for broken in (np.full(cols, np.nan), -np.ones(cols)):

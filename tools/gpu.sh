@@ -21,7 +21,7 @@ quick)
   timeout 900 python tools/quick_bench.py "$@" 2>&1 | tee gpurun_out/quick.log ;;
 tests)
   if [ $# -eq 0 ]; then set -- tests; fi
-  timeout 1500 python -m pytest "$@" -m gpu -x -q 2>&1 | tee gpurun_out/pytest_gpu.log | tail -15 ;;
+  timeout 1500 python -m pytest "$@" -m gpu -x -q --timeout 300 2>&1 | tee gpurun_out/pytest_gpu.log | tail -15 ;;
 batch)
   { echo "== batch tests"; timeout 900 python -m pytest tests/test_gpu_batch_device.py -m gpu -x -q 2>&1 | tail -8
     echo "== c3 shards"; timeout 600 python tools/quick_bench.py c3shards "$@"; } 2>&1 | tee gpurun_out/batch.log ;;
@@ -34,7 +34,7 @@ check)
   TAG=${1:-r2}
   nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt
   lscpu | grep -E "Model name|^CPU\(s\)|Thread|Core|Socket" > gpurun_out/host_cpu.txt
-  timeout 1800 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_$TAG.log
+  timeout 1800 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu_$TAG.log
   timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke_$TAG.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke_$TAG.log
   timeout 1200 python bench.py > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err; echo "bench rc=$?" >> gpurun_out/bench_$TAG.err
   timeout 900 python bench.py --impl reference > gpurun_out/bench_ref_$TAG.json 2> gpurun_out/bench_ref_$TAG.err

@@ -11,6 +11,7 @@ LIB_PATH = os.environ.get("B200LSAP_LIB") or os.path.join(PKG, "libb200lsap.so")
 
 COL_MAJOR, ROW_MAJOR = 0, 1
 IPC_HANDLE_BYTES = 64
+NOALLOC_MAX_ELEMS = 2097152
 OK, ERR_SHAPE, ERR_INFEASIBLE, ERR_MAX_ROUNDS, ERR_CUDA, ERR_ARG, ERR_NO_DEVICE = range(7)
 
 
@@ -88,6 +89,9 @@ SIGNATURES = {
                                            C.POINTER(Stats)]),
     "b200lsap_multi_solve_batch_f32": (C.c_int, [_H, _P, _i64, C.c_int32, C.c_int32, C.c_int, C.POINTER(Options), _P,
                                                  C.POINTER(Stats)]),
+    "b200lsap_solve_batch_noalloc_f32": (C.c_int, [C.c_int, _P, _P, _i64, C.c_int32, C.c_int32, C.c_int, C.POINTER(Options),
+                                                   _P, _P]),
+    "b200lsap_noalloc_last_error": (C.c_char_p, []),
     "b200lsap_debug_counters": (C.c_int, [_H, C.POINTER(_i64), C.c_int]),
     "b200lsap_host_alloc": (C.c_void_p, [_i64]),
     "b200lsap_host_free": (None, [_P]),

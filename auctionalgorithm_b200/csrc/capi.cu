@@ -2339,3 +2339,160 @@ int b200lsap_multi_solve_batch_f32(b200lsap_multi* m, const float* a, int64_t ba
 
 } // extern "C"
 
+// =============================================================================================
+// Allocation-free batched solve (no counterpart in the reference).
+// For callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it.  Everything the batched kernel needs besides the caller's input and output lives in ONE file-scope device
+// array: its control block (hand-out counter, status, statistics) and, for column-major problems, the staging area
+// of the re-layout pass.  Every GPU that loads the library holds these B200LSAP_NOALLOC_SCRATCH_BYTES until exit.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address is taken once per device,
+// with that device current, by cudaGetSymbolAddress, and only that pointer is handed to kernels and memsets.
+// =============================================================================================
+namespace
+{
+
+constexpr size_t kNoAllocCtrlBytes = 256; // BatchCtrl at the front, staging behind it (256-byte aligned)
+static_assert(sizeof(BatchCtrl) <= kNoAllocCtrlBytes, "control block does not fit its slot");
+static_assert(B200LSAP_NOALLOC_SCRATCH_BYTES == kNoAllocCtrlBytes + (size_t)B200LSAP_NOALLOC_MAX_ELEMS * sizeof(float),
+              "header and library disagree on the scratch size");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200LSAP_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocDevice
+{
+    bool ready = false;
+    unsigned char* scratch = nullptr; // device address of g_noalloc_scratch on this device
+    int num_sms = 0;
+    int per_sm_filter[16] = {};       // resident CTAs per SM of the filtered kernels, 0: not asked yet
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+char g_noalloc_err[256] = "";
+
+int noalloc_fail(int status, const char* what, cudaError_t e = cudaSuccess)
+{
+    if (e != cudaSuccess)
+        snprintf(g_noalloc_err, sizeof g_noalloc_err, "%s: %s", what, cudaGetErrorString(e));
+    else
+        snprintf(g_noalloc_err, sizeof g_noalloc_err, "%s", what);
+    return status;
+}
+
+#define NA(call)                                                                                                   \
+    do                                                                                                             \
+    {                                                                                                              \
+        cudaError_t e_ = (call);                                                                                   \
+        if (e_ != cudaSuccess)                                                                                     \
+            return noalloc_fail(B200LSAP_ERR_CUDA, #call, e_);                                                     \
+    } while (0)
+
+} // namespace
+
+extern "C" {
+
+const char* b200lsap_noalloc_last_error(void) { return g_noalloc_err; }
+
+int b200lsap_solve_batch_noalloc_f32(int device, void* cuda_stream, const float* a_dev, int64_t batch, int32_t rows,
+                                     int32_t cols, int layout, const b200lsap_options* opts, int32_t* row_to_col_dev,
+                                     int32_t* status_dev)
+{
+    if (!a_dev || !row_to_col_dev)
+        return noalloc_fail(B200LSAP_ERR_ARG, "null pointer");
+    if (layout != B200LSAP_COL_MAJOR && layout != B200LSAP_ROW_MAJOR)
+        return noalloc_fail(B200LSAP_ERR_ARG, "layout must be 0 or 1");
+    if (batch < 0 || rows < 1 || cols < 1 || rows > cols || rows > kBatchMaxRows || cols > kBatchMaxCols)
+        return noalloc_fail(B200LSAP_ERR_SHAPE, "batched mode needs 1 <= rows <= cols, rows <= 32, cols <= 64");
+    const bool convert = layout == B200LSAP_COL_MAJOR && rows > 1 && cols > 1;
+    const int64_t total = batch * rows * cols;
+    if (convert && total > (int64_t)B200LSAP_NOALLOC_MAX_ELEMS)
+        return noalloc_fail(B200LSAP_ERR_SHAPE,
+                            "column-major batch exceeds B200LSAP_NOALLOC_MAX_ELEMS coefficients (the static staging area); "
+                            "pass row-major problems or split the batch");
+    b200lsap_options o;
+    b200lsap_options_default(&o);
+    if (opts)
+        o = *opts;
+    if (!(o.eps_multiplier > 0))
+        return noalloc_fail(B200LSAP_ERR_ARG, "eps_multiplier must be positive");
+    if (device < 0)
+        NA(cudaGetDevice(&device));
+    if (device >= kNoAllocMaxDevices)
+        return noalloc_fail(B200LSAP_ERR_ARG, "device index out of range");
+    NA(cudaSetDevice(device));
+    NoAllocDevice& d = g_noalloc_dev[device];
+    if (!d.ready)
+    {
+        // set-up, once per device, with that device current (none of these calls allocates)
+        void* p = nullptr;
+        NA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        NA(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, device));
+        d.scratch = static_cast<unsigned char*>(p);
+        d.ready = true;
+    }
+    if (batch == 0)
+        return B200LSAP_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    BatchCtrl* ctl = reinterpret_cast<BatchCtrl*>(d.scratch);
+    float* staging = reinterpret_cast<float*>(d.scratch + kNoAllocCtrlBytes);
+    // the array keeps the last call's contents: the control block must start at zero (counter, status, statistics)
+    NA(cudaMemsetAsync(ctl, 0, sizeof(BatchCtrl), stream));
+    const float* src = a_dev;
+    if (convert)
+    {
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 1023) / 1024, (int64_t)d.num_sms * 8));
+        k_batch_to_row_major<<<grid, 256, 0, stream>>>(a_dev, staging, batch, rows, cols);
+        src = staging;
+    }
+    BatchParams P;
+    P.a = src;
+    P.row2col = row_to_col_dev;
+    P.batch = batch;
+    P.rows = rows;
+    P.cols = cols;
+    P.eps = o.eps_multiplier / (double)cols;
+    P.max_bids = o.max_rounds > 0 ? (int)(o.max_rounds > 0x7fffffff ? 0x7fffffff : o.max_rounds) : 1000000;
+    P.ctl = ctl;
+    P.status = &ctl->status;
+    P.cap = o.batch_bid_cap > 0 ? o.batch_bid_cap : (o.batch_bid_cap < 0 ? 0x7fffffff : 96);
+    P.chunk = 16;
+    using BatchKernel = void (*)(BatchParams);
+    if (cols % 4 == 0 && ((uintptr_t)src & 15) == 0)
+    {
+        constexpr int kFW = 4, kFC = 4;
+#define B200LSAP_NA_FILTER(M) k_auction_batch_filter<M, true, kFW, kFC>, k_auction_batch_filter<M, false, kFW, kFC>
+        static const BatchKernel kf[16] = {B200LSAP_NA_FILTER(1), B200LSAP_NA_FILTER(2), B200LSAP_NA_FILTER(3),
+                                           B200LSAP_NA_FILTER(4), B200LSAP_NA_FILTER(5), B200LSAP_NA_FILTER(6),
+                                           B200LSAP_NA_FILTER(7), B200LSAP_NA_FILTER(8)};
+        const int kM = (cols + 7) / 8;
+        const int which = 2 * (kM - 1) + (cols % 8 == 0 ? 0 : 1);
+        const size_t fsmem = kFW * batch_filter_warp_bytes(kM);
+        if (d.per_sm_filter[which] == 0)
+        {
+            NA(cudaFuncSetAttribute(kf[which], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+            NA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.per_sm_filter[which], kf[which], kFW * 32, fsmem));
+            if (d.per_sm_filter[which] < 1)
+                return noalloc_fail(B200LSAP_ERR_CUDA, "k_auction_batch_filter does not fit on an SM");
+        }
+        const int64_t fgrid = std::min<int64_t>((batch + 16 * kFW - 1) / (16 * kFW), (int64_t)d.per_sm_filter[which] * d.num_sms);
+        kf[which]<<<(int)std::max<int64_t>(fgrid, 1), kFW * 32, fsmem, stream>>>(P);
+    }
+    else
+    {
+#define B200LSAP_NA_STREAM4(C) k_auction_batch_stream<C, 4, 20>
+        static const BatchKernel k4[16] = {B200LSAP_NA_STREAM4(1),  B200LSAP_NA_STREAM4(2),  B200LSAP_NA_STREAM4(3),
+                                           B200LSAP_NA_STREAM4(4),  B200LSAP_NA_STREAM4(5),  B200LSAP_NA_STREAM4(6),
+                                           B200LSAP_NA_STREAM4(7),  B200LSAP_NA_STREAM4(8),  B200LSAP_NA_STREAM4(9),
+                                           B200LSAP_NA_STREAM4(10), B200LSAP_NA_STREAM4(11), B200LSAP_NA_STREAM4(12),
+                                           B200LSAP_NA_STREAM4(13), B200LSAP_NA_STREAM4(14), B200LSAP_NA_STREAM4(15),
+                                           B200LSAP_NA_STREAM4(16)};
+        const int64_t sgrid = std::min<int64_t>((batch + 7) / 8, (int64_t)20 * d.num_sms);
+        k4[(cols + 3) / 4 - 1]<<<(int)sgrid, 32, 0, stream>>>(P);
+    }
+    NA(cudaGetLastError());
+    if (status_dev)
+        NA(cudaMemcpyAsync(status_dev, &ctl->status, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+    return B200LSAP_OK;
+}
+
+} // extern "C"
+

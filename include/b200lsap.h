@@ -309,6 +309,35 @@ int b200lsap_multi_solve_batch_f32(b200lsap_multi* multi, const float* a, int64_
                                    int layout, const b200lsap_options* opts, int32_t* row_to_col,
                                    b200lsap_stats* stats);
 
+/*
+ * Allocation-free batched solve.  This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same problems, same kernels and same result as
+ * b200lsap_solve_batch_device_f32, but without a handle and without any allocation: it calls no cudaMalloc,
+ * cudaFree or allocating library routine.  Its scratch — the launch's control block and, for column-major problems
+ * (layout 0), the staging area of the re-layout pass — is ONE file-scope device array of
+ * B200LSAP_NOALLOC_SCRATCH_BYTES (8 MiB + 256 B) that every GPU which loads the library holds until exit.
+ *   - a_dev, row_to_col_dev (int32[batch*rows]) and status_dev (nullable int32: 0, or the b200lsap_status of a failed
+ *     problem, whose rows read -1) are DEVICE pointers owned by the caller; device < 0 = the current device;
+ *     cuda_stream = the cudaStream_t to enqueue on (NULL: the legacy default stream).
+ *   - asynchronous: it returns once the work is enqueued (nothing is copied to the host, nothing synchronises), so it
+ *     may be captured into a CUDA graph; the result is ready when the stream reaches that point.
+ *   - limit: a column-major batch may hold at most B200LSAP_NOALLOC_MAX_ELEMS (2 097 152) coefficients
+ *     (batch * rows * cols; 1365 problems of 32 x 48); beyond it the call is refused with B200LSAP_ERR_SHAPE.
+ *     Row-major problems (layout 1) use only the control block and have no such limit.
+ *   - every call on a device shares the array: calls that OVERLAP on the GPU (two streams, two threads, a graph
+ *     replayed beside another call) race on it — serialise them.  The control block is cleared on the stream at the
+ *     start of every call; the staging area keeps the last call's contents and is overwritten before it is read.
+ *   - opts (nullable): eps_multiplier, max_rounds (bid watchdog per problem) and batch_bid_cap are honoured.
+ * Argument errors are returned at once; their text is in b200lsap_noalloc_last_error().
+ */
+#define B200LSAP_NOALLOC_MAX_ELEMS 2097152
+#define B200LSAP_NOALLOC_SCRATCH_BYTES (256 + 4 * B200LSAP_NOALLOC_MAX_ELEMS)
+int b200lsap_solve_batch_noalloc_f32(int device, void* cuda_stream, const float* a_dev, int64_t batch, int32_t rows,
+                                     int32_t cols, int layout, const b200lsap_options* opts, int32_t* row_to_col_dev,
+                                     int32_t* status_dev);
+const char* b200lsap_noalloc_last_error(void);
+
 /* Full-sweep bidding pass for measurement: every row bids once, nothing is updated.
  * use_last_prices = 0: the state a solve starts from (zero prices, no candidate lists: the first
  * sweep of the first eps phase).  1: the state the handle's last dense solve left: its prices and,

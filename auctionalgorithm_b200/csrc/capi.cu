@@ -325,6 +325,7 @@ struct DensePlan
     bool eps_auto;     // first eps of the scaling schedule from the data (k_probe / k_schedule; fp32 only)
     double eps_factor;
     int use_cache;
+    int asym_phases = 0;               // rows < cols: the last this-many phases end with the price repair (run_dense)
     const double* prices_in = nullptr; // warm start (options.prices_in): host pointer on the host entries, device otherwise
     bool prices_on_host = false;
 };
@@ -455,6 +456,7 @@ int make_plan(b200lsap_handle* h, int64_t rows, int64_t cols, const b200lsap_opt
     // against 6 582 cold: imported prices save the price DISCOVERY of the early phases, not the phases themselves)
     bool scaling = o.eps_scaling < 0 ? (rows == cols) : (o.eps_scaling != 0);
     plan.prices_in = o.prices_in;
+    plan.asym_phases = o.eps_scaling == 2 ? 1 : kMaxPhases;
     if (scaling && rows != cols && o.driver != 0)
         return fail(h, B200LSAP_ERR_ARG, "eps scaling on rows < cols needs the persistent driver (driver = 0)");
     plan.eps.clear();
@@ -539,6 +541,7 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.dry = 0;
     s.narrow_after = 0;
     s.phase_cut = 0;
+    s.asym_repair = 0;
     return s;
 }
 
@@ -582,6 +585,11 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
     }
     if (const char* e = getenv("B200LSAP_PHASE_CUT"))
         s.phase_cut = plan.driver == 0 ? atoi(e) : 0;
+    // rows < cols with scaled eps or imported prices: the price post-condition is kept at the end of every phase
+    static const int repair_env = getenv("B200LSAP_ASYM_PHASES") ? atoi(getenv("B200LSAP_ASYM_PHASES")) : 0; // developer knob
+    s.asym_repair = (plan.driver == 0 && plan.rows < plan.cols && (plan.prices_in || plan.eps.size() > 1 || resume))
+                        ? (repair_env > 0 ? repair_env : plan.asym_phases)
+                        : 0;
     std::vector<double> eps = plan.eps;
     if (resume)
     {
@@ -668,7 +676,9 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
                 // needs another one
                 for (int batch_no = 0; batch_no < 64; batch_no++)
                 {
-                    for (int p = 0; p < n_phases; p++)
+                    // (a repaired phase hands over to k_narrow once more: a launch pair extra per phase covers that;
+                    // launches that find the solve done return at once)
+                    for (int p = 0; p < n_phases * (s.asym_repair ? 2 : 1); p++)
                     {
                         CU(cudaLaunchCooperativeKernel((const void*)k_auction_persistent<T>, dim3(grid), dim3(kThreads),
                                                        args, 0, h->stream));
@@ -762,6 +772,7 @@ int run_dense_once(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& 
         stats->eps_first = hc->eps[0];
         stats->cache_hits = hc->cache_hits;
         stats->cache_misses = hc->cache_misses;
+        stats->warm_fallback = hc->repairs; // floor raises at the ends of phases (rows < cols)
     }
     if (hc->status != 0)
         return fail(h, hc->status, b200lsap_status_string(hc->status));
@@ -822,7 +833,7 @@ int run_dense(b200lsap_handle* h, const T* A, int64_t ld, const DensePlan& plan,
             return rc;
     }
     if (stats)
-        stats->warm_fallback = repairs;
+        stats->warm_fallback = h->h_ctrl->repairs + repairs; // in-kernel (per phase) + this safety net
     return B200LSAP_OK;
 }
 

@@ -1037,6 +1037,81 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_persistent(const __grid
         const int n = ctrl->count[cur];
         if (n == 0 || (n <= s.phase_cut && phase >= 0 && phase + 1 < n_phases))
         {
+            if (n == 0 && s.asym_repair && phase >= 0 && phase + s.asym_repair >= n_phases)
+            {
+                // End of a phase on rows < cols: no unassigned object may be priced above an assigned one
+                // (AuctionCommon.h:347-354 with lambda = the lowest assigned price; what the reference's reverse auction
+                // is for, Auction.h:346-469).  When one is, every price below the highest unassigned price F rises to F —
+                // the collective move of the cols - rows dummy bidders of the equivalent square problem; prices stay
+                // monotone, so candidate lists, row caches and bid slots stay valid — and the rows whose object was
+                // raised bid again AT THIS PHASE'S eps.  Done per phase, the last phase starts from prices whose floor
+                // is already right and has little left to repair.
+                if (tid == 0)
+                {
+                    ctrl->lam_hi = 0ull;
+                    ctrl->lam_lo = (unsigned long long)__double_as_longlong(1e300);
+                }
+                grid.sync();
+                double hi = 0.0, lo = 1e300;
+                for (long long j = tid; j < s.cols; j += n_threads)
+                {
+                    const double p = s.prices[j];
+                    if (s.owner[j] < 0)
+                        hi = fmax(hi, p);
+                    else
+                        lo = fmin(lo, p);
+                }
+#pragma unroll
+                for (int sft = 16; sft >= 1; sft >>= 1)
+                {
+                    hi = fmax(hi, __shfl_xor_sync(kFullMask, hi, sft));
+                    lo = fmin(lo, __shfl_xor_sync(kFullMask, lo, sft));
+                }
+                if (lane == 0)
+                {
+                    // non-negative doubles order like their bits
+                    atomicMax(&s.ctrl->lam_hi, (unsigned long long)__double_as_longlong(hi));
+                    atomicMin(&s.ctrl->lam_lo, (unsigned long long)__double_as_longlong(lo));
+                }
+                grid.sync();
+                const double F = __longlong_as_double((long long)ctrl->lam_hi), L = __longlong_as_double((long long)ctrl->lam_lo);
+                if (F > L)
+                {
+                    for (long long j = tid; j < s.cols; j += n_threads)
+                        if (s.prices[j] < F)
+                        {
+                            s.prices[j] = F;
+                            s.pricesf[j] = (float)F;
+                            const int o = s.owner[j];
+                            if (o >= 0)
+                            {
+                                s.row2col[o] = -1;
+                                s.owner[j] = -1;
+                            }
+                        }
+                    if (tid == 0)
+                        ctrl->repairs = ctrl->repairs + 1;
+                    grid.sync();
+                    const long long up = ((long long)s.rows + 31) & ~31ll;
+                    for (long long i = tid; i < up; i += n_threads)
+                    {
+                        const bool push = i < s.rows && s.row2col[i] < 0;
+                        const unsigned m = __ballot_sync(kFullMask, push);
+                        if (m)
+                        {
+                            int base = 0;
+                            if (lane == 0)
+                                base = atomicAdd(&s.ctrl->count[cur], __popc(m));
+                            base = __shfl_sync(kFullMask, base, 0);
+                            if (push)
+                                s.list[cur][base + __popc(m & ((1u << lane) - 1))] = (int)i;
+                        }
+                    }
+                    grid.sync();
+                    small_rounds = 0;
+                    continue; // the same phase goes on with the unassigned rows
+                }
+            }
             if (phase + 1 >= n_phases)
                 break;
             phase++;

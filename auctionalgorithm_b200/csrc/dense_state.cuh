@@ -91,6 +91,10 @@ struct DenseCtrl
     double amax;            // max |a(i,j)| of the matrix being solved (k_absmax)
     double eps[kMaxPhases]; // eps[n_phases-1] = eps_multiplier / cols
     unsigned long long shard_x; // fused sharded solve: exchanges so far (handed from CTA 0 back to the grid)
+    // rows < cols with eps scaling or a warm start: price post-condition at the end of every phase (asym_repair)
+    unsigned long long lam_hi;  // bits of the highest price of an unassigned object
+    unsigned long long lam_lo;  // bits of the lowest price of an assigned object
+    long long repairs;          // floor raises so far
 };
 
 // Slack of the single-precision filter of scan_segment_filtered: with |a| <= amax, 0 <= p <= pbound,
@@ -154,6 +158,8 @@ template <typename T> struct DenseState
     CacheEnt<T>* cache;    // [rows][kCacheK] (column, a), best first
     RowCacheHdr* cache_hdr; // [rows]
     int use_cache;         // 1: narrow rounds answer from the row cache (persistent driver)
+    int asym_repair;       // R > 0 (the last R phases repair): rows < cols and prices may break "no unassigned object priced above an assigned one"
+                           // (eps scaling, warm start): checked and repaired at the end of every eps phase
     int phase_cut;         // an eps phase other than the last ends as soon as at most this many rows are unassigned
                            // (the next phase drops every assignment anyway; only the last phase decides the result)
     int narrow_after;      // row caches: a phase plays this many of its small rounds as wide rounds before it pays for

@@ -69,7 +69,7 @@ class Handle:
         if eps_multiplier is not None:
             o.eps_multiplier = eps_multiplier
         if eps_scaling is not None:
-            o.eps_scaling = {True: 1, False: 0}.get(eps_scaling, eps_scaling)
+            o.eps_scaling = int(eps_scaling)  # True / False / -1 / 2 (include/b200lsap.h)
         if eps_start is not None:
             o.eps_start = eps_start
         if eps_factor is not None:

@@ -61,13 +61,17 @@ typedef struct b200lsap_handle b200lsap_handle;
 typedef struct
 {
     double eps_multiplier; /* final eps = eps_multiplier / cols; default 1e-5 (internal.h:16) */
-    int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on.  On with
-                              rows < cols (persistent driver only): after the last phase the post-condition of
-                              AuctionCommon.h:347-354 — no unassigned object priced above an assigned one, what the
-                              reference's reverse auction and lambda are for (Auction.h:346-469) — is restored by
-                              raising every price below the highest unassigned price to it (prices stay monotone),
-                              unassigning the rows whose object was raised and letting them bid again at the final
-                              eps, until it holds (stats.warm_fallback = number of such repairs) */
+    int32_t eps_scaling;   /* -1 auto (on iff rows == cols), 0 off (the reference's fixed eps), 1 on, 2 on with the
+                              asymmetric repair after the last phase only.  On with rows < cols (persistent driver
+                              only): a forward auction with scaled eps may end a phase with an unassigned object
+                              priced above an assigned one, which breaks the post-condition of
+                              AuctionCommon.h:347-354 — what the reference's reverse auction and lambda are for
+                              (Auction.h:346-469).  It is restored at the end of every phase (1) or of the last one
+                              (2) by raising every price below the highest unassigned price to it (prices stay
+                              monotone), unassigning the rows whose object was raised and letting them bid again at
+                              that phase's eps (stats.warm_fallback = number of such repairs).  Measured: 1 pays
+                              where the fixed eps crawls (rank-one 2048 x 2052: 2.87 M rounds -> 0.11 M) and costs
+                              ~3x the rounds where it does not (uniform noise); 2 costs ~5 % and gains nothing. */
     double eps_start;      /* first eps of the scaling schedule; <= 0: default (an eighth of the mean spread
                               of a row's best ~36 values, measured on 128 sampled rows, at most 0.25).
                               A default first phase that runs over its work budget

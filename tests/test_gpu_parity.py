@@ -118,8 +118,11 @@ def test_error_statuses_instead_of_hanging(handle):
     with pytest.raises(ab.B200LsapError) as e:
         handle.solve(a)
     assert e.value.status == ab.ERR_INFEASIBLE
+    # eps scaling on rows < cols is legal since round 2 (the price post-condition is repaired); only the host-driven
+    # driver refuses it
+    assert sorted(handle.solve(np.ones((4, 6), np.float32), eps_scaling=True)) == [0, 1, 2, 3]
     with pytest.raises(ab.B200LsapError) as e:
-        handle.solve(np.ones((4, 6), np.float32), eps_scaling=True)
+        handle.solve(np.ones((4, 6), np.float32), eps_scaling=True, driver=1)
     assert e.value.status == ab.ERR_ARG
     # two rows that can only take the same column: the reference spins, we stop at the watchdog
     b = np.zeros((2, 3), np.float32)

@@ -1514,8 +1514,15 @@ int batch_host_enqueue(b200lsap_handle* h, const float* a, int64_t batch, int ro
         if (rc)
             return rc;
         CU(cudaEventRecord(h->ev_done[k], h->stream));
+    }
+    // downloads in a loop of their own: a copy into PAGEABLE host memory blocks the calling thread until its kernel has
+    // finished, which would hold back the uploads of the later chunks if it were enqueued between them
+    for (int k = 0; k < n_chunks; k++)
+    {
+        const int64_t b0 = batch * k / n_chunks, nb = batch * (k + 1) / n_chunks - b0;
         CU(cudaStreamWaitEvent(h->down, h->ev_done[k], 0));
-        CU(cudaMemcpyAsync(row_to_col + b0 * rows, out, nb * rows * sizeof(int32_t), cudaMemcpyDeviceToHost, h->down));
+        CU(cudaMemcpyAsync(row_to_col + b0 * rows, h->batch_out.as<int32_t>() + b0 * rows, nb * rows * sizeof(int32_t),
+                           cudaMemcpyDeviceToHost, h->down));
     }
     CU(cudaEventRecord(h->ev[3], h->down));
     return B200LSAP_OK;

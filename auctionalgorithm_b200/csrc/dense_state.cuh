@@ -95,6 +95,8 @@ struct DenseCtrl
     unsigned long long lam_hi;  // bits of the highest price of an unassigned object
     unsigned long long lam_lo;  // bits of the lowest price of an assigned object
     long long repairs;          // floor raises so far
+    int solo_seq;               // episodes that one CTA has played alone so far (the others doze on this word)
+    int pad3;
 };
 
 // Slack of the single-precision filter of scan_segment_filtered: with |a| <= amax, 0 <= p <= pbound,

@@ -457,6 +457,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
     unsigned long long* epoch_p = reinterpret_cast<unsigned long long*>(cm.box[cm.rank] + 3072);
     const unsigned long long epoch = *epoch_p;
     unsigned long long x = 0; // exchanges of this solve so far
+    int solo = ctrl->solo_seq; // single-CTA episodes so far (the same in every CTA)
     const long long cap_items = max((long long)total_warps + 64, 4ll * g.rows); // entries of l.partial (alloc_state)
 
     // max |a| over all shards (slack of the single-precision filter) is taken from the first sweep: every row bids
@@ -494,6 +495,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
         if (!first_sweep && n <= kThreads && (long long)n * l.cols4 * (long long)sizeof(T) <= small_bytes)
         {
             // ---- the rest of this phase on CTA 0 ------------------------------------------------------------------
+            solo++;
+            if (blockIdx.x != 0)
+                solo_wait(g.ctrl, solo); // doze instead of polling the grid barrier (dense_kernels.cuh)
             if (blockIdx.x == 0)
             {
                 int m = n;
@@ -531,6 +535,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                     ctrl->bids = bids;
                     ctrl->shard_x = x;
                 }
+                solo_done(g.ctrl, solo);
             }
             grid.sync();
             cur = ctrl->cur;

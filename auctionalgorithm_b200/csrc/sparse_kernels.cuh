@@ -383,6 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_csr(const __grid_consta
     __shared__ CsrNarrowShared<T> nsh;
 
     int cur = 0, phase = 0;
+    int solo = ctrl->solo_seq; // narrow episodes so far (the same in every CTA)
     const int n_phases = ctrl->n_phases;
     const long long max_rounds = ctrl->max_rounds;
     long long wide_rounds = 0, wide_bids = 0;
@@ -417,6 +418,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_csr(const __grid_consta
         if (n <= narrow_limit)
         {
             // ---- CTA 0 finishes the phase: the same rounds with block barriers ----------------------
+            solo++;
+            if (blockIdx.x != 0)
+                solo_wait(s.ctrl, solo); // doze instead of hammering the grid barrier (dense_kernels.cuh)
             if (blockIdx.x == 0)
             {
                 long long b = 0;
@@ -431,6 +435,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_auction_csr(const __grid_consta
                     ctrl->count[cur] = 0;
                     __threadfence();
                 }
+                solo_done(s.ctrl, solo);
             }
             grid.sync();
             if (ctrl->status != 0)

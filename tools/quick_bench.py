@@ -111,6 +111,17 @@ if __name__ == "__main__":
         for _ in range(3):
             st = h.solve_batch_device(t.data_ptr(), 1, 32, 48, out.data_ptr())
         print(f"monster alone: {st['ms_solve']*1e3:.1f} us", flush=True)
+    if "c3host" in which:   # the host entry of the batched mode: pinned input, pageable and pinned output
+        n = 1 << 18
+        t = torch.empty((n, 32, 48), dtype=torch.float32, device="cuda")
+        h.generate_device(t.data_ptr(), n, 32, 48, 48, 1, 1)
+        host = torch.empty((n, 32, 48), dtype=torch.float32, pin_memory=True); host.copy_(t); torch.cuda.synchronize()
+        a = host.numpy()
+        for _ in range(2):
+            h.solve_batch(a)
+        for rep in range(3):
+            t0 = time.perf_counter(); r = h.solve_batch(a); sec = time.perf_counter() - t0
+            print(f"c3 host entry: {n/sec/1e6:.2f} M problems/s, {a.nbytes/sec/1e9:.1f} GB/s H2D, {sec*1e3:.2f} ms", flush=True)
     if "c3caps" in which:
         for cap in (-1, 64, 96, 128, 192):
             batch_shards(shards=3, batch_bid_cap=cap)

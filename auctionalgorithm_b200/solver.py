@@ -175,7 +175,7 @@ class Handle:
         layout=COL_MAJOR and C-contiguous storage of the transposed problems)."""
         a = np.ascontiguousarray(a, dtype=np.float32)
         batch, rows, cols = a.shape
-        out = np.full((batch, rows), -1, np.int32)
+        out = np.empty((batch, rows), np.int32)  # every entry is written by the library (-1 for a failed problem)
         st = Stats()
         o = self._opts(**options)
         rc = self._lib.b200lsap_solve_batch_f32(self._h, a.ctypes.data, batch, rows, cols, layout, C.byref(o),

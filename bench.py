@@ -254,11 +254,12 @@ def run_reference(args):
         v = statistics.mean(vals)
         print(json.dumps({
             "impl": "reference", "metric": "mht_32x48_problems_per_s", "value": v, "unit": "problems/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": None,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * (n // 4) / v,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"c3: batched MHT data association, 32x48 fp32 problems, seed {SEED}; the reference's "
                                    "Auction<double>::solve once per problem on all host threads (it has no batched "
-                                   "entry and no GPU path: the host does not grow with --gpus)"},
+                                   "entry and no GPU path: the host does not grow with --gpus); a step = a bounded sample of "
+                                   f"{n // 4} problems"},
             "cpu_baseline": dict(last, value=v, unit="problems/s"),
             "e2e": {"value": v, "unit": "problems/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }))

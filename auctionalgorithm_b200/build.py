@@ -44,6 +44,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         cmd.insert(1, "-DB200LSAP_TIMING")
     if os.environ.get("B200LSAP_VAR"):  # developer experiments (dense_cache.cuh)
         cmd.insert(1, "-DB200LSAP_VAR=" + os.environ["B200LSAP_VAR"])
+    for d in os.environ.get("B200LSAP_DEFINES", "").split():  # developer experiments: "-DB200LSAP_SOLO_MAX=3 ..."
+        cmd.insert(1, d)
     if os.environ.get("B200LSAP_OUT"):
         cmd[cmd.index("-o") + 1] = os.environ["B200LSAP_OUT"]
     if verbose:

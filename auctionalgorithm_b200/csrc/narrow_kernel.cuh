@@ -33,6 +33,10 @@ namespace b200lsap
 constexpr int kNarrowThreads = 512;
 constexpr int kNarrowWarps = kNarrowThreads / 32;
 constexpr int kMissMark = -2;
+#ifndef B200LSAP_SOLO_MAX
+#define B200LSAP_SOLO_MAX 2
+#endif
+constexpr int kSoloMax = B200LSAP_SOLO_MAX; // rounds with 2..kSoloMax bidders are played by warp 0 alone
 constexpr int kNarrowHashBits = 9, kNarrowHash = 1 << kNarrowHashBits; // >= 2 kNarrowMax slots
 
 template <typename T> struct NarrowKShared
@@ -46,7 +50,7 @@ template <typename T> struct NarrowKShared
     int warp_count[kNarrowWarps];
     int hcol[kNarrowHash];  // resolve of a round with more than 32 bidders: column of the slot, -1 empty
     int hbest[kNarrowHash]; //   bidder index of the best bid for it so far, -1 none
-    int qn, stop, nmiss, served;
+    int qn, stop, nmiss, served, served_bids;
     double pmax;
     Top2<T> res; // result of the fallback scan
 };
@@ -471,7 +475,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
     const long long work_budget = ctrl->phase_budget;
     long long work = ctrl->phase_work; // the wide rounds of this phase
     bool escalated = false;
-    long long bids = 0, misses = 0, fast = 0;
+    long long bids = 0, misses = 0, fast = 0, solo_rounds = 0;
 #ifdef B200LSAP_TIMING
     long long acc2 = 0, acc3 = 0, acc4 = 0, acc5 = 0, acc6 = 0, acc7 = 0;
     long long bk_c0 = 0, bk_c1 = 0, bk_c2 = 0, bk_c3 = 0, bk_r0 = 0, bk_r1 = 0, bk_r2 = 0, bk_r3 = 0;
@@ -508,6 +512,133 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
     } while (0)
 #else
 #define NTICK(k)
+#endif
+#ifndef B200LSAP_NO_SOLO_ROUNDS
+        if (n >= 2 && n <= kSoloMax)
+        {
+            // ---- two to four bidders: warp 0 alone plays the Jacobi rounds (bidders evaluated two at a time, the two
+            // dependency chains interleaved; resolved in registers) for as long as at least two bidders remain: no block
+            // barrier and no shared-memory exchange per round (a general round with <= 4 bidders cost 1900 cycles, two
+            // barriers among them).  Same rounds as the general path: same winner rule, same order of the next list.
+            if (warp == 0)
+            {
+                int r[kSoloMax];
+#pragma unroll
+                for (int u = 0; u < kSoloMax; u++)
+                    r[u] = u < n ? q[u] : -1;
+                int m = n, served = 0, served_bids = 0;
+                for (;;)
+                {
+                    Top2<T> t[kSoloMax];
+                    int prev[kSoloMax];
+                    bool ok = true;
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u += 2)
+                    {
+                        if (u + 1 < m)
+                        {
+                            const int ii[2] = {r[u], r[u + 1]};
+                            Top2<T> tt[2];
+                            int pp[2];
+                            bool hh[2];
+                            narrow_eval2<kSmem, T>(s, prices_s, owner_s, ii, lane, tt, pp, hh);
+                            t[u] = tt[0], t[u + 1] = tt[1];
+                            prev[u] = pp[0], prev[u + 1] = pp[1];
+                            ok = ok && hh[0] && hh[1];
+                        }
+                        else if (u < m)
+                        {
+                            ok = narrow_eval<kSmem, false, T>(s, prices_s, owner_s, r[u], lane, t[u], prev[u]) && ok;
+                        }
+                    }
+                    if (!ok)
+                        break; // a miss: the general round below scans the row
+                    double bid[kSoloMax];
+                    bool win[kSoloMax];
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                        bid[u] = u < m ? (double)t[u].a - t[u].w + eps : 0.0; // Auction.h:250
+                    // highest bid per column, lowest row among equal bids
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                    {
+                        win[u] = u < m;
+#pragma unroll
+                        for (int v = 0; v < kSoloMax; v++)
+                            if (v != u && v < m && u < m && t[v].j == t[u].j &&
+                                (bid[v] > bid[u] || (bid[v] == bid[u] && r[v] < r[u])))
+                                win[u] = false;
+                    }
+                    if (lane == 0)
+                    {
+                        double top = 0.0;
+#pragma unroll
+                        for (int u = 0; u < kSoloMax; u++)
+                            if (u < m)
+                            {
+                                s.profits[r[u]] = t[u].w - eps; // Auction.h:253
+                                if (win[u])
+                                {
+                                    narrow_commit<kSmem, T>(s, prices_s, owner_s, r[u], t[u].j, bid[u], prev[u]);
+                                    top = fmax(top, bid[u]);
+                                }
+                            }
+                        if (top > sh.pmax)
+                            sh.pmax = top;
+                    }
+                    served++;
+                    served_bids += m;
+                    // next list, in bidder order: a loser stays, a winner hands its place to the row it evicted
+                    int nr[kSoloMax], mn = 0;
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                        nr[u] = -1;
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                    {
+                        const int push = u < m ? (win[u] ? prev[u] : r[u]) : -1;
+                        if (push >= 0)
+                        {
+#pragma unroll
+                            for (int k = 0; k < kSoloMax; k++)
+                                if (k == mn)
+                                    nr[k] = push;
+                            mn++;
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                        r[u] = nr[u];
+                    m = mn;
+                    __syncwarp(); // lane 0's shared-memory prices before the next gather
+                    if (m < 2 || rounds + served >= budget || (esc_ok && work + served > work_budget))
+                        break;
+                }
+                if (lane == 0)
+                {
+#pragma unroll
+                    for (int u = 0; u < kSoloMax; u++)
+                        if (u < m)
+                            q[u] = r[u];
+                    sh.qn = m;
+                    sh.served = served;
+                    sh.served_bids = served_bids;
+                }
+            }
+            __syncthreads();
+            const int served = sh.served;
+            rounds += served;
+            bids += sh.served_bids;
+            work += served;
+            solo_rounds += served;
+            n = sh.qn;
+            if (served > 0 || n < 2 || n > kSoloMax)
+            {
+                __syncthreads(); // sh.served is rewritten by the next episode
+                continue;
+            }
+            // a miss in the very first of these rounds: fall through to the general round
+        }
 #endif
         if (n == 1)
         {
@@ -799,6 +930,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->cache_hits += bids - misses;
         ctrl->cache_misses += misses;
         ctrl->gs_bids += fast; // bids placed by the one-bidder path (included in rounds and bids)
+        ctrl->dbg[12] += solo_rounds; // rounds with 2..kSoloMax bidders played by warp 0 alone (b200lsap_debug_counters)
         if (sh.pmax > ctrl->pmax)
             ctrl->pmax = sh.pmax;
 #ifdef B200LSAP_TIMING

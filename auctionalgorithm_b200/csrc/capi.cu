@@ -542,6 +542,8 @@ template <typename T> DenseState<T> bind_state(b200lsap_handle* h, const T* A, i
     s.narrow_after = 0;
     s.phase_cut = 0;
     s.asym_repair = 0;
+    static const int every = getenv("B200LSAP_CACHE_EVERY_PHASE") ? atoi(getenv("B200LSAP_CACHE_EVERY_PHASE")) : 0;
+    s.rebuild_caches_every_phase = every;
     return s;
 }
 

@@ -96,7 +96,8 @@ struct DenseCtrl
     unsigned long long lam_lo;  // bits of the lowest price of an assigned object
     long long repairs;          // floor raises so far
     int solo_seq;               // episodes that one CTA has played alone so far (the others doze on this word)
-    int pad3;
+    int cache_fresh;            // row caches: 1 = built in this solve and the last narrow phase hardly missed (they hold across
+                                // phases: prices only rise, so every bound stays valid); 0 = (re)build before the next one
 };
 
 // Slack of the single-precision filter of scan_segment_filtered: with |a| <= amax, 0 <= p <= pbound,
@@ -160,6 +161,7 @@ template <typename T> struct DenseState
     CacheEnt<T>* cache;    // [rows][kCacheK] (column, a), best first
     RowCacheHdr* cache_hdr; // [rows]
     int use_cache;         // 1: narrow rounds answer from the row cache (persistent driver)
+    int rebuild_caches_every_phase; // 1: the round-1 behaviour (developer knob B200LSAP_CACHE_EVERY_PHASE)
     int asym_repair;       // R > 0 (the last R phases repair): rows < cols and prices may break "no unassigned object priced above an assigned one"
                            // (eps scaling, warm start): checked and repaired at the end of every eps phase
     int phase_cut;         // an eps phase other than the last ends as soon as at most this many rows are unassigned

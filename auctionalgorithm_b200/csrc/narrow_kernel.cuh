@@ -929,6 +929,7 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->narrow_rounds += rounds;
         ctrl->cache_hits += bids - misses;
         ctrl->cache_misses += misses;
+        ctrl->cache_fresh = misses * 64 <= bids ? 1 : 0; // next phase: keep the caches unless this one missed > 1.5 %
         ctrl->gs_bids += fast; // bids placed by the one-bidder path (included in rounds and bids)
         ctrl->dbg[12] += solo_rounds; // rounds with 2..kSoloMax bidders played by warp 0 alone (b200lsap_debug_counters)
         if (sh.pmax > ctrl->pmax)

@@ -476,6 +476,10 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
     long long work = ctrl->phase_work; // the wide rounds of this phase
     bool escalated = false;
     long long bids = 0, misses = 0, fast = 0, solo_rounds = 0;
+    // (an entry read before its row's cache was rebuilt stays valid: bounds hold for ever, prices only rise)
+    int pre_row = -1;
+    CacheEnt<T> pre_e = make_ent<T>(0, T(0));
+    RowCacheHdr pre_h{0.0, 0, 0};
 #ifdef B200LSAP_TIMING
     long long acc2 = 0, acc3 = 0, acc4 = 0, acc5 = 0, acc6 = 0, acc7 = 0;
     long long bk_c0 = 0, bk_c1 = 0, bk_c2 = 0, bk_c3 = 0, bk_r0 = 0, bk_r1 = 0, bk_r2 = 0, bk_r3 = 0;
@@ -726,7 +730,33 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
             if (b1 < n)
                 narrow_eval2<kSmem, T>(s, prices_s, owner_s, i, lane, t, prev, hit);
             else
-                hit[0] = narrow_eval<kSmem, false, T>(s, prices_s, owner_s, i[0], lane, t[0], prev[0]);
+            {
+                // The row this bid evicts bids in the next round, and — a winner hands its place in the list to the row it
+                // evicted — usually at this very position, i.e. in this very warp: its cache entry is requested now, so that
+                // the L2 round trip runs behind this round's barriers and resolve instead of opening the next evaluation.
+                CacheEnt<T> e;
+                RowCacheHdr h;
+                if (b == warp && pre_row == i[0])
+                {
+                    e = pre_e;
+                    h = pre_h;
+                }
+                else
+                {
+                    e = s.cache[(long long)i[0] * kCacheK + lane];
+                    h = s.cache_hdr[i[0]];
+                }
+                hit[0] = narrow_eval_regs<kSmem, false, T>(s, prices_s, owner_s, e, h, lane, t[0], prev[0], nullptr);
+                if (b == warp)
+                {
+                    pre_row = prev[0];
+                    if (prev[0] >= 0)
+                    {
+                        pre_e = s.cache[(long long)prev[0] * kCacheK + lane];
+                        pre_h = s.cache_hdr[prev[0]];
+                    }
+                }
+            }
             if (lane == 0)
             {
 #pragma unroll

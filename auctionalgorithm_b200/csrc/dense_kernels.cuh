@@ -460,11 +460,40 @@ __device__ __forceinline__ void bid_phase_pairs(const DenseState<T>& s, const in
         asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_addr(&ps.bar[threadIdx.x])));
 }
 
+// (narrow_kernel.cuh, included below)
+template <bool kSmem, bool kChase, typename T>
+__device__ __forceinline__ bool narrow_eval(const DenseState<T>& s, const double* prices_s, const int* owner_s, int i,
+                                            int lane, Top2<T>& t, int& prev, long long* evp);
+
 template <typename T>
 __device__ __forceinline__ void bid_phase(const DenseState<T>& s, const int* __restrict__ list, int n, double eps,
                                           double amax, double pmax, int warp_global, int total_warps, int lane)
 {
     const float margin = filter_margin(amax, pmax);
+    if (s.use_cache && s.ctrl->cache_fresh && !s.dry)
+    {
+        // Row caches that a narrow phase has just used with hardly a miss (they hold across eps phases: prices only
+        // rise) answer the WIDE rounds too: a warp evaluates its bidder's 32 cached columns at the current prices
+        // (256 bytes from L2) and, when the second best of them beats the bound on everything else, has the very bid a
+        // scan of the 64 KB row would place.  The rare miss scans the row on the spot.  The first sweep of a phase then
+        // reads 4 MB instead of the whole matrix.
+        for (int b = warp_global; b < n; b += total_warps)
+        {
+            const int i = list[b];
+            Top2<T> t;
+            int prev;
+            if (!narrow_eval<false, false, T>(s, nullptr, nullptr, i, lane, t, prev, nullptr))
+            {
+                const float thr0 = cand_threshold(s, i, margin, lane);
+                t = scan_segment<T>(s, s.A + (long long)i * s.ld, margin, thr0, 0, s.cols4, lane);
+                top2_warp_reduce_sparse(t);
+                t = rescue_scan(s, i, t, lane);
+            }
+            if (lane == 0)
+                submit_bid(s, i, t, eps, pmax);
+        }
+        return;
+    }
     if (pair_rounds(n, total_warps, s.cols4, s.min_seg, s.sweep_split))
     {
         bid_phase_pairs<T>(s, list, n, eps, margin, pmax, warp_global, total_warps, lane);

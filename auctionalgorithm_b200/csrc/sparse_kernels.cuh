@@ -125,6 +125,7 @@ template <typename T> struct CsrNarrowShared
     int hbest[kCsrHash];     //             bidder index of the best bid so far, -1 none
     Top2<T> part[kWarpsPerBlock]; // long rows: partial results of the row's segments
     int qn[2];               // bidders in q[0] / q[1]
+    int served;              // bids placed by the one-bidder chain of warp 0
     int status;
     double pmax;
 };
@@ -249,6 +250,62 @@ __device__ __noinline__ long long csr_narrow_episode(const DenseState<T>& s, con
         const int n = sh.qn[buf];
         if (n == 0 || rounds >= budget)
             break;
+        if (n == 1)
+        {
+            // ---- one bidder: warp 0 alone, bid after bid along the eviction chain (the dense path's k_narrow does the
+            // same): scan the row, bid, evict, go on with the evicted row; no block barrier, no hash table.  These are
+            // the same Jacobi rounds (a round with one bidder has one winner), so prices come out identical.
+            if (warp == 0)
+            {
+                int i = sh.q[buf][0], served = 0, left = 1;
+                for (;;)
+                {
+                    const Top2<T> t = csr_scan_range<T, false>(m, s.prices, m.ptr[i], m.ptr[i + 1], lane);
+                    if (t.j < 0)
+                        break; // every value at or below -1e6, or no entry: the general round below deals with it
+                    const double bid = (double)t.a - t.w + eps; // Auction.h:250
+                    const int prev = s.owner[t.j];
+                    __syncwarp();
+                    if (lane == 0)
+                    {
+                        s.profits[i] = t.w - eps; // Auction.h:253
+                        s.owner[t.j] = i;
+                        s.prices[t.j] = bid;      // Auction.h:259
+                        s.row2col[i] = t.j;
+                        if (prev >= 0)
+                            s.row2col[prev] = -1; // Auction.h:270
+                        if (bid > sh.pmax)
+                            sh.pmax = bid;
+                    }
+                    served++;
+                    if (prev < 0)
+                    {
+                        left = 0;
+                        break;
+                    }
+                    i = prev;
+                    if (rounds + served >= budget)
+                        break;
+                    __syncwarp(); // lane 0's price and owner before the next row's gathers
+                }
+                if (lane == 0)
+                {
+                    sh.q[buf][0] = i;
+                    sh.qn[buf] = left;
+                    sh.served = served;
+                }
+            }
+            __syncthreads();
+            const int served = sh.served;
+            rounds += served;
+            bids += served;
+            if (served > 0)
+            {
+                __syncthreads(); // sh.served is rewritten by the next chain
+                continue;
+            }
+            // nothing placed (a row that needs the rescue scan): the general round below takes it
+        }
         const int* q = sh.q[buf];
         int* qnext = sh.q[buf ^ 1];
         // ---- bids ----------------------------------------------------------------------------------

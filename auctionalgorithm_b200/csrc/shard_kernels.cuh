@@ -384,9 +384,19 @@ __device__ __forceinline__ void shard_bid_phase(const DenseState<T>& l, const Sh
             r.j = t.j >= 0 ? t.j + col0 : -1;
             r.row = i;
             shard_slot(cm, lane, buf, cm.rank)[i] = r; // lane q writes rank q's mailbox
-            __threadfence_system();                    // ... and only the writers pay for a system fence
+            // (no fence here: one system-scope fence per CTA after the phase — shard_publish — and the release of the
+            // flag order every record before the flag; a fence per record cost ~40 us per round)
         }
     }
+}
+
+// End of a CTA's bid phase: its records (peer stores by many of its threads) are pushed out to system scope once, by one
+// thread, after a block barrier; the grid sync and the st.release.sys of the flag that follow are cumulative over it.
+__device__ __forceinline__ void shard_publish()
+{
+    __syncthreads();
+    if (threadIdx.x == 0)
+        __threadfence_system();
 }
 
 // Every rank, identically: merge the ranks' records of each bidder (rank order = column order, so top2_merge's
@@ -510,6 +520,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                     float unused = 0.f;
                     shard_bid_phase<T>(l, cm, col0, g.list[cur], m, buf, false, filter_margin(amax, pmax), threadIdx.x >> 5,
                                        kWarpsPerBlock, lane, unused, cap_items);
+                    shard_publish();
                     __syncthreads();
                     const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status);
                     if (ok_x)
@@ -562,6 +573,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                 atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->amax),
                           (unsigned long long)__double_as_longlong((double)amax_seen));
         }
+        shard_publish();
         grid.sync();
         const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status, first_sweep ? &ctrl->amax : nullptr);
         if (first_sweep)

@@ -560,6 +560,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
             ctrl->count[cur ^ 1] = 0;
         const int buf = (int)(x & 1);
         float amax_seen = 0.f;
+#ifdef B200LSAP_TIMING
+        long long tq = clock64();
+#define SHTICK(k)                                                                                                  \
+    do                                                                                                             \
+    {                                                                                                              \
+        if (tid == 0 && n <= kThreads && !first_sweep)                                                             \
+        {                                                                                                          \
+            const long long now_ = clock64();                                                                      \
+            g.ctrl->dbg[k] += now_ - tq;                                                                           \
+            tq = now_;                                                                                             \
+        }                                                                                                          \
+    } while (0)
+#else
+#define SHTICK(k)
+#endif
         const double pmax = fmax(ctrl->pmax, amax);
         shard_bid_phase<T>(l, cm, col0, g.list[cur], n, buf, first_sweep, filter_margin(amax, pmax), warp_global, total_warps,
                            lane, amax_seen, cap_items);
@@ -573,8 +588,44 @@ __global__ void __launch_bounds__(kThreads, 1) k_shard_persistent(const __grid_c
                 atomicMax(reinterpret_cast<unsigned long long*>(&g.ctrl->amax),
                           (unsigned long long)__double_as_longlong((double)amax_seen));
         }
+        SHTICK(0);
         shard_publish();
+        SHTICK(1);
         grid.sync();
+        SHTICK(2);
+        if (!first_sweep && n <= kThreads)
+        {
+            // A round whose bidders fit one CTA's threads: CTA 0 alone waits for the ranks' flags, merges and resolves
+            // (block barriers), the others go straight to the grid sync that ends the round: two grid syncs per round
+            // instead of three.
+            ++x;
+            if (blockIdx.x == 0)
+            {
+                const bool ok_small = shard_exchange(cm, epoch + x, &g.ctrl->status);
+                SHTICK(3);
+                if (ok_small)
+                    shard_merge_phase<T>(g, cm, g.list[cur], n, buf, eps, pmax, threadIdx.x, kThreads);
+                __threadfence();
+                __syncthreads();
+                SHTICK(4);
+                if (ctrl->status == 0)
+                    resolve_phase<T>(g, g.list[cur], n, g.list[cur ^ 1], &g.ctrl->count[cur ^ 1], threadIdx.x, kThreads, lane);
+                __threadfence();
+                SHTICK(5);
+            }
+            grid.sync();
+            SHTICK(6);
+#ifdef B200LSAP_TIMING
+            if (tid == 0)
+                g.ctrl->dbg[7] += 1;
+#endif
+            if (ctrl->status != 0)
+                break;
+            cur ^= 1;
+            rounds++;
+            bids += n;
+            continue;
+        }
         const bool ok_x = shard_exchange(cm, epoch + ++x, &g.ctrl->status, first_sweep ? &ctrl->amax : nullptr);
         if (first_sweep)
         {

@@ -239,7 +239,10 @@ int b200lsap_generate_shard_device_f32(b200lsap_handle* handle, float* a_dev, in
  *     all-gather of the records, rank-major: gathered[r*n + b]      (the caller's: NCCL, NVLink)
  *     shard_resolve  -> merges, resolves, updates the replica; n_next bidders remain
  * until n_next == 0; then shard_next_phase (eps scaling, square problems) and, when it reports
- * no more phases, shard_finish.  begin returns this rank's max |a|; the caller must set the
+ * no more phases, shard_finish.  STREAM CONTRACT: shard_bid enqueues its kernel on the handle's stream and returns
+ * without synchronising, and shard_resolve reads `gathered` on that stream: the caller's exchange must run on the SAME
+ * stream (b200lsap_set_stream with the stream of its collective, e.g. torch's current stream — what
+ * auctionalgorithm_b200.sharded.CudaShardEngine does) or be ordered against it with events.  begin returns this rank's max |a|; the caller must set the
  * maximum over all ranks with shard_set_amax before the first bid (it scales the slack of the
  * single-precision filter).  auctionalgorithm_b200/sharded.py drives this with torch.distributed.
  */

@@ -48,6 +48,19 @@ def test_sharded_matches_golden_and_replicas_agree(handle, oracle_lib, name, wor
     assert handle.last_stats["rounds"] == st0["rounds"] and handle.last_stats["bids"] == st0["bids"]
 
 
+def test_sharded_host_driven_on_a_non_default_torch_stream(oracle_lib):
+    # the exchange (here torch.cat) and the handle's kernels must share one stream: the engine binds the handle to
+    # torch's CURRENT stream when it is made (the tests used to depend on launch timing)
+    import torch
+    g = np.load(f"{parity.GOLDEN_DIR}/auction_512x768_s1.npz")
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        a, res = _run(oracle_lib, 512, 768, 1, 3)
+    side.synchronize()
+    for r2c, p, st in res:
+        assert np.array_equal(r2c.cpu().numpy().astype(np.int64), parity.golden_row_to_col(g))
+
+
 def test_sharded_with_zeros_and_a_shard_without_edges(oracle_lib):
     rows, cols = 64, 512
     a = oracle_lib.generate(rows, cols, 11)

@@ -122,6 +122,8 @@ if __name__ == "__main__":
         for rep in range(3):
             t0 = time.perf_counter(); r = h.solve_batch(a); sec = time.perf_counter() - t0
             print(f"c3 host entry: {n/sec/1e6:.2f} M problems/s, {a.nbytes/sec/1e9:.1f} GB/s H2D, {sec*1e3:.2f} ms", flush=True)
+    if "c3s3" in which:     # three shards (0, 1, 2) only: A/B runs with environment knobs
+        batch_shards(shards=3)
     if "c3caps" in which:
         for cap in (-1, 64, 96, 128, 192):
             batch_shards(shards=3, batch_bid_cap=cap)

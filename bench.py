@@ -613,8 +613,8 @@ def main_single(args, handle, torch, dist, ab, np, peak, peak_src):
 
     # ---- bidding kernel alone: the roofline ------------------------------------------------------------------
     # Two states: the one a solve starts from (zero prices, no candidate lists: the cold sweep every solve pays) and
-    # the one the solves above left on the handle (their prices and the rows' candidate lists: what the first sweep
-    # of every eps phase after the first starts from; 7 of the 8 full sweeps of this solve).
+    # the one the solves above left on the handle (their prices and the rows' candidate lists: what a full sweep of a
+    # later eps phase starts from when it has to scan, i.e. when the row caches were not reusable).
     warm_ms, cold_ms = [], []
     for _ in range(3 + 5):
         ms, nbytes = handle.bid_sweep_device(a_dev.data_ptr(), rows, cols, cols, use_last_prices=True)
@@ -630,7 +630,7 @@ def main_single(args, handle, torch, dist, ab, np, peak, peak_src):
                 "ms_per_launch": cold, "algorithmic_bytes_per_launch": nbytes,
                 "frac_of_read_only_peak": nbytes / cold / 1e6 / READ_ONLY_PEAK_GBS,
                 "read_only_peak_gbs": READ_ONLY_PEAK_GBS,
-                "warm_sweep": {"what": "same kernel on the prices and candidate lists a solve leaves (7 of its 8 full sweeps)",
+                "warm_sweep": {"what": "same kernel on the prices and candidate lists a solve leaves (kept for comparison: since the row caches are reused across phases the later full sweeps of a solve no longer scan the matrix at all)",
                                "ms_per_launch": warm, "achieved": nbytes / warm / 1e6, "frac": nbytes / warm / 1e6 / peak,
                                "frac_of_read_only_peak": nbytes / warm / 1e6 / READ_ONLY_PEAK_GBS},
                 "note": "the copy peak counts read + write bytes; a read-only stream reaches ~7.0 TB/s on this part, so "

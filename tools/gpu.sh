@@ -12,6 +12,8 @@
 #   benchn N TAG           bench.py on N GPUs launched as the driver does (gpurun --gpus N)
 #   ncu    KERNEL TAG ARGS one `ncu --set full` capture of the first launch matching KERNEL in quick_bench ARGS,
 #                          taken only after the same command exited 0 without ncu
+#   final  TAG             last call of a round on a short budget: the newest GPU test alone, one `ncu --set full` capture of
+#                          k_narrow (launches 6-8 of a C4 solve, after the same command ran without ncu), then the whole suite
 #   sanitize [TOOLS]       compute-sanitizer memcheck / racecheck / synccheck over tools/sanitize_cases.py
 cd "${GRAFT_REPO_ROOT:-$(dirname "$0")/..}" || exit 1
 mkdir -p gpurun_out
@@ -53,6 +55,16 @@ ncu)
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s ${NCU_SKIP:-1} -c 1 -f -o gpurun_out/$TAG \
       python tools/quick_bench.py "$@" > gpurun_out/ncu_$TAG.log 2>&1
   cat gpurun_out/ncu_plain_$TAG.log; tail -3 gpurun_out/ncu_$TAG.log; ls -la gpurun_out/*.ncu-rep ;;
+final)
+  TAG=${1:-r2d}
+  timeout 200 python -m pytest tests/test_gpu_sharded.py -m gpu -x -q -k non_default_torch_stream > gpurun_out/pytest_new_$TAG.log 2>&1
+  echo "pytest rc=$?" >> gpurun_out/pytest_new_$TAG.log; tail -3 gpurun_out/pytest_new_$TAG.log
+  timeout 120 python tools/quick_bench.py c4t > gpurun_out/ncu_plain_$TAG.log 2>&1 && \
+  timeout 240 ncu --set full --clock-control none --import-source on -k regex:k_narrow -s 5 -c 3 -f -o gpurun_out/${TAG}_knarrow \
+      python tools/quick_bench.py c4t > gpurun_out/ncu_$TAG.log 2>&1
+  cat gpurun_out/ncu_plain_$TAG.log; tail -3 gpurun_out/ncu_$TAG.log; ls -la gpurun_out/*.ncu-rep
+  timeout 400 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_$TAG.log 2>&1
+  echo "pytest rc=$?" >> gpurun_out/pytest_gpu_$TAG.log; tail -4 gpurun_out/pytest_gpu_$TAG.log ;;
 sanitize)
   if [ $# -eq 0 ]; then set -- memcheck racecheck synccheck; fi
   for tool in "$@"; do

@@ -14,6 +14,8 @@
 #                          taken only after the same command exited 0 without ncu
 #   final  TAG             last call of a round on a short budget: the newest GPU test alone, one `ncu --set full` capture of
 #                          k_narrow (launches 6-8 of a C4 solve, after the same command ran without ncu), then the whole suite
+#   pick   NAMES...        A/B of side builds build_timing/NAME.so against the tree's build on the C4 solve (quick_bench c4t sq), then
+#                          the whole GPU suite under the fastest of them (B200LSAP_LIB) if it beats the tree's build
 #   sanitize [TOOLS]       compute-sanitizer memcheck / racecheck / synccheck over tools/sanitize_cases.py
 cd "${GRAFT_REPO_ROOT:-$(dirname "$0")/..}" || exit 1
 mkdir -p gpurun_out
@@ -65,6 +67,25 @@ final)
   cat gpurun_out/ncu_plain_$TAG.log; tail -3 gpurun_out/ncu_$TAG.log; ls -la gpurun_out/*.ncu-rep
   timeout 400 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_$TAG.log 2>&1
   echo "pytest rc=$?" >> gpurun_out/pytest_gpu_$TAG.log; tail -4 gpurun_out/pytest_gpu_$TAG.log ;;
+pick)
+  : > gpurun_out/pick.log
+  best=tree; best_ms=""
+  for name in tree "$@"; do
+    lib=""; [ "$name" != tree ] && lib=$PWD/build_timing/$name.so
+    echo "== $name" >> gpurun_out/pick.log
+    B200LSAP_LIB=$lib timeout 150 python tools/quick_bench.py c4t sq >> gpurun_out/pick.log 2>&1
+    ms=$(grep "dense 16384x16384" gpurun_out/pick.log | tail -1 | sed -E 's/.*: ([0-9.]+) ms rounds.*/\1/')
+    echo "   -> $name c4 $ms ms" >> gpurun_out/pick.log
+    case "$name" in timing*|nm*) continue ;; esac
+    if [ -z "$best_ms" ]; then best_ms=$ms; tree_ms=$ms
+    elif [ -n "$ms" ] && python -c "import sys; sys.exit(0 if float('$ms') < float('$best_ms') else 1)"; then best=$name; best_ms=$ms; fi
+  done
+  echo "== fastest: $best ($best_ms ms; tree $tree_ms ms)" >> gpurun_out/pick.log
+  cat gpurun_out/pick.log
+  if [ "$best" != tree ] && [ -z "$NO_SUITE" ]; then
+    B200LSAP_LIB=$PWD/build_timing/$best.so timeout 400 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_pick_$best.log 2>&1
+    echo "pytest rc=$?" >> gpurun_out/pytest_gpu_pick_$best.log; tail -6 gpurun_out/pytest_gpu_pick_$best.log
+  fi ;;
 sanitize)
   if [ $# -eq 0 ]; then set -- memcheck racecheck synccheck; fi
   for tool in "$@"; do

@@ -969,7 +969,14 @@ __global__ void __launch_bounds__(kNarrowThreads, 1) k_narrow(const __grid_const
         ctrl->dbg[8] += rounds;
         ctrl->dbg[9] += bids;
         ctrl->dbg[1] += fast;
-#if B200LSAP_VAR == 12 // rounds and cycles of the general rounds by number of bidders
+#if B200LSAP_VAR == 13 // sections of a one-bidder bid: wait for the cache entry, price gather, reductions, winner's data
+        for (int k = 0; k < 4; k++)
+        {
+            ctrl->dbg[2 + k] += g_ev[k];
+            g_ev[k] = 0;
+        }
+        ctrl->dbg[6] += acc2;
+#elif B200LSAP_VAR == 12 // rounds and cycles of the general rounds by number of bidders
         ctrl->dbg[2] += bk_r0; ctrl->dbg[3] += bk_c0;
         ctrl->dbg[4] += bk_r1; ctrl->dbg[5] += bk_c1;
         ctrl->dbg[6] += bk_r2; ctrl->dbg[7] += bk_c2;

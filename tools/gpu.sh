@@ -83,7 +83,7 @@ pick)
   echo "== fastest: $best ($best_ms ms; tree $tree_ms ms)" >> gpurun_out/pick.log
   cat gpurun_out/pick.log
   if [ "$best" != tree ] && [ -z "$NO_SUITE" ]; then
-    B200LSAP_LIB=$PWD/build_timing/$best.so timeout 400 python -m pytest tests -m gpu -x -q --timeout 300 > gpurun_out/pytest_gpu_pick_$best.log 2>&1
+    B200LSAP_LIB=$PWD/build_timing/$best.so timeout 400 python -m pytest tests -m gpu -x -q --timeout 300 ${PYTEST_N:+-n $PYTEST_N} > gpurun_out/pytest_gpu_pick_$best.log 2>&1
     echo "pytest rc=$?" >> gpurun_out/pytest_gpu_pick_$best.log; tail -6 gpurun_out/pytest_gpu_pick_$best.log
   fi ;;
 sanitize)
